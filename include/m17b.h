@@ -1,0 +1,188 @@
+/*
+ * m17b.h -- C ABI of libm17b.so, the B200-native many-channel M17 demodulator.
+ *
+ * The reference (mobilinkd/m17-cxx-demod) is a header-only C++ library with no C
+ * ABI and no plugin mechanism; its demodulation entry points are
+ *
+ *   M17Demodulator<float>::M17Demodulator(callback_t)      M17Demodulator.h:180-182
+ *   M17Demodulator<float>::operator()(float sample)        M17Demodulator.h:216,656-753
+ *   M17Demodulator<float>::diagnostics(cb) / locked()      M17Demodulator.h:198-212
+ *   M17FrameDecoder::callback_t(output_buffer_t const&, int viterbi_cost)
+ *                                                          M17FrameDecoder.h:68-77,98
+ *   the m17-demod stdin loop `demod(sample / 41067.0)`     apps/m17-demod.cpp:484-490
+ *
+ * This ABI is what a binding for that path binds instead: one context owns N
+ * independent 48 kS/s int16 baseband streams resident on one GPU;
+ * m17b_submit() replaces N x samples calls of operator()(float), and
+ * m17b_drain() returns, per stream in chronological order, one m17b_frame per
+ * invocation the reference would have made of callback_t -- bit for bit the
+ * same output_buffer_t contents and viterbi cost.  The header-only facade
+ * include/m17cxx_b200/M17Demodulator.h re-creates the reference's class API on
+ * top of these calls.
+ *
+ * Conventions: plain C types; caller-allocated outputs; return 0 on success or
+ * a negative M17B_E* code (m17b_strerror()); no exceptions cross the ABI; calls
+ * on one context must be externally serialised; a context owns all of its
+ * device memory and CUDA streams.  There is no CPU fallback: without a CUDA
+ * device m17b_create() fails with M17B_ENODEV.
+ */
+#ifndef M17B_H
+#define M17B_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M17B_VERSION 0x00010000u
+
+/* error codes */
+#define M17B_OK        0
+#define M17B_EINVAL   -1   /* bad argument                                         */
+#define M17B_ENODEV   -2   /* no usable CUDA device / driver                       */
+#define M17B_ENOMEM   -3   /* device or host allocation failed                     */
+#define M17B_ECUDA    -4   /* a CUDA call or kernel failed (m17b_last_cuda_error)  */
+#define M17B_EOVERFLOW -5  /* frame record ring overflowed: drain more often       */
+#define M17B_ESTATE   -6   /* internal invariant violated (counter `faults`)       */
+
+/* m17b_config.flags */
+#define M17B_FIR_FMA     0x1u  /* matched filter accumulates with fused multiply-add: outputs within
+                                  1e-5 relative of the reference but not bit-identical.  Default
+                                  (flag clear) is the reference's exact mul-then-add order
+                                  (FirFilter.h:36-40), bit-identical filter outputs.            */
+#define M17B_INVERT      0x2u  /* `sample *= -1` before scaling (apps/m17-demod.cpp:488, -i)   */
+#define M17B_PROFILE     0x4u  /* record CUDA events around every kernel (m17b_get_profile)    */
+
+/* m17b_submit location */
+#define M17B_HOST    0         /* samples points to host memory (pinned for full overlap)      */
+#define M17B_DEVICE  1         /* samples points to device memory on the context's GPU         */
+
+/* frame types == M17FrameDecoder::FrameType (M17FrameDecoder.h:53) */
+enum {
+    M17B_FRAME_LSF = 0, M17B_FRAME_LICH = 1, M17B_FRAME_STREAM = 2,
+    M17B_FRAME_BASIC_PACKET = 3, M17B_FRAME_FULL_PACKET = 4, M17B_FRAME_BERT = 5
+};
+
+typedef struct m17b_ctx m17b_ctx;
+
+typedef struct m17b_config {
+    uint32_t n_streams;        /* independent channels owned by this context               */
+    int32_t  device;           /* CUDA device ordinal                                      */
+    uint32_t max_chunk;        /* largest samples-per-stream a single m17b_submit may carry */
+    uint32_t flags;            /* M17B_FIR_FMA | M17B_INVERT | M17B_PROFILE                */
+    uint32_t frame_capacity;   /* frame records buffered on the device between drains
+                                  (0: n_streams * (max_chunk / 960 + 8))                   */
+    uint32_t reserved[3];
+} m17b_config;
+
+/*
+ * One record per reference callback invocation: output_buffer_t
+ * (M17FrameDecoder.h:68-77) + the int viterbi_cost argument.  `payload` is the
+ * 26-byte union {lich[6], stream[18], packet[26], bert[25]} exactly as the
+ * reference's callback sees it (bytes past the active member are whatever an
+ * earlier frame left there, like in the reference); `lsf` is output_buffer.lsf.
+ */
+typedef struct m17b_frame {
+    uint32_t stream;           /* channel index in [0, n_streams)                          */
+    uint32_t seq;              /* ordinal of this callback within its stream               */
+    uint64_t sample_pos;       /* 0-based index of the input sample that fired it          */
+    int32_t  viterbi_cost;
+    uint8_t  type;             /* M17B_FRAME_*                                             */
+    uint8_t  pad[3];
+    uint8_t  payload[26];
+    uint8_t  lsf[30];
+} m17b_frame;                  /* 80 bytes */
+
+/* The arguments of the reference's diagnostic_callback_t (M17Demodulator.h:144,
+ * 681-685,746-750), sampled for one stream at its current position. */
+typedef struct m17b_diag {
+    int32_t  dcd;
+    float    evm;
+    float    deviation;
+    float    offset;
+    int32_t  locked;
+    float    clock;
+    int32_t  sample_index;
+    int32_t  sync_index;
+    int32_t  clock_index;
+    int32_t  viterbi_cost;
+    uint64_t samples;          /* samples of this stream processed so far                  */
+} m17b_diag;
+
+typedef struct m17b_counters {
+    uint64_t samples;          /* samples demodulated over all streams                     */
+    uint64_t frames[6];        /* callbacks by M17B_FRAME_* type                           */
+    uint64_t lsf_crc_fail;     /* LSF frames whose CRC16 failed (M17FrameDecoder.h:175)    */
+    uint64_t golay_fail;       /* LICH frames with an uncorrectable Golay word (:195)      */
+    uint64_t faults;           /* internal invariant violations (must stay 0)              */
+    uint64_t dropped;          /* frame records lost to ring overflow (must stay 0)        */
+} m17b_counters;
+
+/* Accumulated device time per kernel (CUDA events on the launching stream),
+ * only when M17B_PROFILE is set. */
+typedef struct m17b_profile {
+    double   fir_ms;     uint64_t fir_launches;     uint64_t fir_samples;    /* matched filter: outputs computed */
+    double   scan_ms;    uint64_t scan_launches;    uint64_t scan_samples;   /* sync/clock/slicer scan           */
+    double   decode_ms;  uint64_t decode_launches;  uint64_t decode_frames;  /* Viterbi/Golay/CRC frame decode   */
+    double   aux_ms;     uint64_t aux_launches;                              /* history tail upkeep              */
+    double   h2d_ms;     uint64_t h2d_bytes;
+    double   d2h_ms;     uint64_t d2h_bytes;
+} m17b_profile;
+
+uint32_t    m17b_version(void);
+const char* m17b_strerror(int code);
+const char* m17b_last_cuda_error(const m17b_ctx* ctx);
+
+int  m17b_device_count(void);
+
+int  m17b_create(const m17b_config* cfg, m17b_ctx** out);
+void m17b_destroy(m17b_ctx* ctx);
+
+/* Pinned host memory helpers (optional; any host pointer works with M17B_HOST). */
+int  m17b_host_alloc(void** ptr, size_t bytes);
+void m17b_host_free(void* ptr);
+/* Device memory on the context's GPU, for callers that stage samples themselves. */
+int  m17b_device_alloc(m17b_ctx* ctx, void** ptr, size_t bytes);
+void m17b_device_free(m17b_ctx* ctx, void* ptr);
+int  m17b_memcpy_h2d(m17b_ctx* ctx, void* dst_device, const void* src_host, size_t bytes);
+
+/*
+ * Feed `samples_per_stream` new int16 samples to every stream: stream s reads
+ * samples[s * stream_stride + 0 .. samples_per_stream).  Asynchronous: returns
+ * once the work is enqueued; the buffer must stay valid until the next
+ * m17b_sync()/m17b_drain().  samples_per_stream <= cfg.max_chunk.
+ */
+int  m17b_submit(m17b_ctx* ctx, const int16_t* samples, size_t samples_per_stream,
+                 size_t stream_stride, int location);
+
+/* Wait for all enqueued work; every stream has then consumed all submitted samples. */
+int  m17b_sync(m17b_ctx* ctx);
+
+/* m17b_sync(), then move up to `cap` frame records to `out`, ordered by (stream, seq).
+ * *n receives the number written; call again while *n == cap. */
+int  m17b_drain(m17b_ctx* ctx, m17b_frame* out, size_t cap, size_t* n);
+
+/* Number of frame records currently waiting on the device (after m17b_sync). */
+int  m17b_pending_frames(m17b_ctx* ctx, size_t* n);
+
+int  m17b_diag_get(m17b_ctx* ctx, uint32_t stream, m17b_diag* out);
+int  m17b_counters_get(m17b_ctx* ctx, m17b_counters* out);
+int  m17b_get_profile(m17b_ctx* ctx, m17b_profile* out, int reset);
+
+/* Kernel-level taps for parity tests: run ONLY the matched filter over
+ * [n_streams][n] int16 (zero history) and return the n filtered floats per stream,
+ * in the filter mode the context was created with. */
+int  m17b_debug_filter(m17b_ctx* ctx, const int16_t* samples_host, size_t n, size_t stream_stride,
+                       float* filtered_host /* [n_streams][n] */, float* scaled_host /* may be NULL */);
+
+/* FP32 pipe microbenchmark: sustained FFMA throughput of the context's GPU in TFLOP/s
+ * (2 flop per FMA), the denominator of the matched filter's roofline fraction.
+ * variant 0: scalar FFMA; 1: packed fma.rn.f32x2; 2: FMUL+FADD pairs. */
+int  m17b_measure_fp32_peak(m17b_ctx* ctx, int variant, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,508 @@
+// m17b_api.cu -- host context behind the C ABI in include/m17b.h.
+//
+// One context = one GPU = N resident streams.  m17b_submit() enqueues, on the
+// context's compute stream,
+//     [H2D copy on the copy stream, double buffered]        (host input only)
+//     fir_kernel over the new samples -> sample ring          (kernel A)
+//     tail_kernel (keeps 160 raw samples of filter history)
+//     R rounds of { scan_kernel ; decode_kernel }             (kernels B, C)
+// where a round lets every stream advance to its next completed frame (or by at
+// most kRoundCap samples).  Frame completions of one stream are >= 1600 samples
+// apart, so R = n/1600 + 2 rounds always reach the head; m17b_sync() verifies
+// that on the device (`lagging`) and adds rounds if it ever is not so.
+#include "m17b_dev.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace m17b;
+
+struct EvPair { cudaEvent_t a, b; int cat; };
+
+struct m17b_ctx {
+    m17b_config cfg{};
+    DevPtrs d{};
+    int16_t* tail[2] = {nullptr, nullptr};
+    int cur_tail = 0;
+    int16_t* stage[2] = {nullptr, nullptr};
+    cudaEvent_t stage_free[2] = {nullptr, nullptr}, stage_ready[2] = {nullptr, nullptr};
+    int cur_stage = 0;
+    cudaStream_t compute = nullptr, copy = nullptr;
+    uint32_t head = 0;
+    unsigned long long head64 = 0;
+    int sm_count = 0;
+    std::string last_error;
+    // frame records pulled from the device, sorted, waiting for m17b_drain
+    std::deque<m17b_frame> ready;
+    // profiling
+    bool profile = false;
+    std::vector<EvPair> ev_live, ev_pool;
+    m17b_profile prof{};
+    Counters host_ctr{};
+};
+
+namespace {
+
+enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H };
+
+int fail(m17b_ctx* c, cudaError_t e, const char* what)
+{
+    if (c) c->last_error = std::string(what) + ": " + cudaGetErrorString(e);
+    return e == cudaErrorMemoryAllocation ? M17B_ENOMEM : M17B_ECUDA;
+}
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(c, e_, #call); } while (0)
+
+uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
+
+void ev_begin(m17b_ctx* c, cudaStream_t s, int cat, EvPair& p)
+{
+    if (!c->profile) return;
+    if (!c->ev_pool.empty()) { p = c->ev_pool.back(); c->ev_pool.pop_back(); }
+    else { cudaEventCreate(&p.a); cudaEventCreate(&p.b); }
+    p.cat = cat;
+    cudaEventRecord(p.a, s);
+}
+
+void ev_end(m17b_ctx* c, cudaStream_t s, EvPair& p)
+{
+    if (!c->profile) return;
+    cudaEventRecord(p.b, s);
+    c->ev_live.push_back(p);
+}
+
+void ev_collect(m17b_ctx* c)
+{
+    for (auto& p : c->ev_live) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            switch (p.cat) {
+            case CAT_FIR: c->prof.fir_ms += ms; break;
+            case CAT_SCAN: c->prof.scan_ms += ms; break;
+            case CAT_DECODE: c->prof.decode_ms += ms; break;
+            case CAT_AUX: c->prof.aux_ms += ms; break;
+            case CAT_H2D: c->prof.h2d_ms += ms; break;
+            default: c->prof.d2h_ms += ms; break;
+            }
+        }
+        c->ev_pool.push_back(p);
+    }
+    c->ev_live.clear();
+}
+
+int run_round(m17b_ctx* c)
+{
+    EvPair p{};
+    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, sizeof(unsigned int), c->compute));
+    ev_begin(c, c->compute, CAT_SCAN, p);
+    launch_scan(c->d, c->head, c->compute);
+    ev_end(c, c->compute, p);
+    c->prof.scan_launches += 1;
+    ev_begin(c, c->compute, CAT_DECODE, p);
+    launch_decode(c->d, c->head, c->head64, c->compute);
+    ev_end(c, c->compute, p);
+    c->prof.decode_launches += 1;
+    CK(cudaGetLastError());
+    return M17B_OK;
+}
+
+int fetch_counters(m17b_ctx* c)
+{
+    CK(cudaMemcpyAsync(&c->host_ctr, c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaStreamSynchronize(c->compute));
+    return M17B_OK;
+}
+
+// Pull every record off the device, order by (stream, seq), append to c->ready.
+int pull_records(m17b_ctx* c)
+{
+    uint32_t n = std::min(c->host_ctr.rec_count, c->d.rec_cap);
+    if (n == 0) return M17B_OK;
+    std::vector<m17b_frame> tmp(n);
+    EvPair p{};
+    ev_begin(c, c->compute, CAT_D2H, p);
+    CK(cudaMemcpyAsync(tmp.data(), c->d.recs, sizeof(m17b_frame) * n, cudaMemcpyDeviceToHost, c->compute));
+    ev_end(c, c->compute, p);
+    CK(cudaMemsetAsync(&c->d.ctr->rec_count, 0, sizeof(unsigned int), c->compute));
+    CK(cudaStreamSynchronize(c->compute));
+    c->prof.d2h_bytes += sizeof(m17b_frame) * n;
+    c->host_ctr.rec_count = 0;
+    std::sort(tmp.begin(), tmp.end(), [](const m17b_frame& a, const m17b_frame& b) {
+        return a.stream != b.stream ? a.stream < b.stream : a.seq < b.seq;
+    });
+    // merge with what is already waiting (older records of a stream come first)
+    if (c->ready.empty()) {
+        c->ready.assign(tmp.begin(), tmp.end());
+    } else {
+        std::vector<m17b_frame> merged(c->ready.size() + tmp.size());
+        std::merge(c->ready.begin(), c->ready.end(), tmp.begin(), tmp.end(), merged.begin(),
+                   [](const m17b_frame& a, const m17b_frame& b) {
+                       return a.stream != b.stream ? a.stream < b.stream : a.seq < b.seq;
+                   });
+        c->ready.assign(merged.begin(), merged.end());
+    }
+    return M17B_OK;
+}
+
+void free_all(m17b_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    if (c->compute) cudaStreamSynchronize(c->compute);
+    if (c->copy) cudaStreamSynchronize(c->copy);
+    for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring);
+    cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
+    cudaFree(c->d.recs); cudaFree(c->d.ctr);
+    for (int i = 0; i != 2; ++i) {
+        cudaFree(c->tail[i]); cudaFree(c->stage[i]);
+        if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
+        if (c->stage_ready[i]) cudaEventDestroy(c->stage_ready[i]);
+    }
+    if (c->compute) cudaStreamDestroy(c->compute);
+    if (c->copy) cudaStreamDestroy(c->copy);
+    delete c;
+}
+
+} // namespace
+
+extern "C" {
+
+uint32_t m17b_version(void) { return M17B_VERSION; }
+
+const char* m17b_strerror(int code)
+{
+    switch (code) {
+    case M17B_OK: return "ok";
+    case M17B_EINVAL: return "invalid argument";
+    case M17B_ENODEV: return "no usable CUDA device";
+    case M17B_ENOMEM: return "out of memory";
+    case M17B_ECUDA: return "CUDA error";
+    case M17B_EOVERFLOW: return "frame record ring overflow";
+    case M17B_ESTATE: return "internal state error";
+    default: return "unknown error";
+    }
+}
+
+const char* m17b_last_cuda_error(const m17b_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+int m17b_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int m17b_create(const m17b_config* cfg, m17b_ctx** out)
+{
+    if (!cfg || !out || cfg->n_streams == 0 || cfg->max_chunk == 0) return M17B_EINVAL;
+    *out = nullptr;
+    int ndev = m17b_device_count();
+    if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return M17B_ENODEV;
+    m17b_ctx* c = new (std::nothrow) m17b_ctx;
+    if (!c) return M17B_ENOMEM;
+    c->cfg = *cfg;
+    c->profile = cfg->flags & M17B_PROFILE;
+    int rc = [&]() -> int {
+        CK(cudaSetDevice(cfg->device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, cfg->device));
+        c->sm_count = prop.multiProcessorCount;
+        CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+
+        DevPtrs& d = c->d;
+        d.n_streams = cfg->n_streams;
+        d.np = (cfg->n_streams + 127u) & ~127u;
+        // ring must hold one submit plus the lag a stream may keep plus the look-back
+        // of the slow filter path / sliding DFT
+        uint32_t need = cfg->max_chunk + kRoundCap + 160 + 16;
+        d.ring_chunks = next_pow2((need + 7) / 8);
+        d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
+                                        : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * (cfg->max_chunk / 960 + 8), 0x7fffffffull);
+        size_t np = d.np;
+        size_t ring_bytes = (size_t) d.ring_chunks * np * 8 * sizeof(float);
+        CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.ring_y, ring_bytes));
+        CK(cudaMalloc(&d.ring_x, ring_bytes));
+        CK(cudaMalloc(&d.corr_ring, 80 * np * sizeof(float)));
+        CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
+        CK(cudaMalloc(&d.fir_snap, (size_t) kTapsUsed * np * sizeof(float)));
+        CK(cudaMalloc(&d.llr, 184 * np * sizeof(int16_t)));
+        CK(cudaMalloc(&d.dec_bytes, 56 * np));
+        CK(cudaMalloc(&d.recs, (size_t) d.rec_cap * sizeof(m17b_frame)));
+        CK(cudaMalloc(&d.ctr, sizeof(Counters)));
+        CK(cudaMemsetAsync(d.ring_y, 0, ring_bytes, c->compute));
+        CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes, c->compute));
+        CK(cudaMemsetAsync(d.corr_ring, 0, 80 * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.sw_samples, 0, 30 * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.fir_snap, 0, (size_t) kTapsUsed * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.llr, 0, 184 * np * sizeof(int16_t), c->compute));
+        CK(cudaMemsetAsync(d.dec_bytes, 0, 56 * np, c->compute));
+        CK(cudaMemsetAsync(d.ctr, 0, sizeof(Counters), c->compute));
+        for (int i = 0; i != 2; ++i) {
+            CK(cudaMalloc(&c->tail[i], (size_t) cfg->n_streams * kTailLen * sizeof(int16_t)));
+            CK(cudaMemsetAsync(c->tail[i], 0, (size_t) cfg->n_streams * kTailLen * sizeof(int16_t), c->compute));
+            CK(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->stage_ready[i], cudaEventDisableTiming));
+        }
+        ConstTables tab;
+        std::vector<uint32_t> golay(2048);
+        build_tables(tab, golay.data());
+        CK(upload_tables(tab, golay.data()));
+        CK(configure_kernels());
+        launch_init_state(d, c->compute);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(c->compute));
+        return M17B_OK;
+    }();
+    if (rc != M17B_OK) {
+        std::fprintf(stderr, "m17b_create: %s\n", c->last_error.c_str());
+        free_all(c);
+        return rc;
+    }
+    *out = c;
+    return M17B_OK;
+}
+
+void m17b_destroy(m17b_ctx* ctx) { free_all(ctx); }
+
+int m17b_host_alloc(void** ptr, size_t bytes)
+{
+    if (!ptr) return M17B_EINVAL;
+    cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocDefault);
+    return e == cudaSuccess ? M17B_OK : M17B_ENOMEM;
+}
+
+void m17b_host_free(void* ptr) { if (ptr) cudaFreeHost(ptr); }
+
+int m17b_device_alloc(m17b_ctx* c, void** ptr, size_t bytes)
+{
+    if (!c || !ptr) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMalloc(ptr, bytes));
+    return M17B_OK;
+}
+
+void m17b_device_free(m17b_ctx* c, void* ptr)
+{
+    if (!c || !ptr) return;
+    cudaSetDevice(c->cfg.device);
+    cudaStreamSynchronize(c->compute);
+    cudaFree(ptr);
+}
+
+int m17b_memcpy_h2d(m17b_ctx* c, void* dst_device, const void* src_host, size_t bytes)
+{
+    if (!c) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpy(dst_device, src_host, bytes, cudaMemcpyHostToDevice));
+    return M17B_OK;
+}
+
+int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, int location)
+{
+    if (!c || !samples || n == 0 || n > c->cfg.max_chunk || stride < n) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t ns = c->cfg.n_streams;
+    const int16_t* dev_in = samples;
+    size_t dev_stride = stride;
+    EvPair p{};
+    if (location == M17B_HOST) {
+        int b = c->cur_stage;
+        c->cur_stage ^= 1;
+        if (!c->stage[b]) CK(cudaMalloc(&c->stage[b], (size_t) ns * c->cfg.max_chunk * sizeof(int16_t)));
+        CK(cudaStreamWaitEvent(c->copy, c->stage_free[b], 0));       // kernels of two submits ago are done with it
+        ev_begin(c, c->copy, CAT_H2D, p);
+        CK(cudaMemcpy2DAsync(c->stage[b], n * sizeof(int16_t), samples, stride * sizeof(int16_t),
+                             n * sizeof(int16_t), ns, cudaMemcpyHostToDevice, c->copy));
+        ev_end(c, c->copy, p);
+        CK(cudaEventRecord(c->stage_ready[b], c->copy));
+        CK(cudaStreamWaitEvent(c->compute, c->stage_ready[b], 0));
+        c->prof.h2d_bytes += (uint64_t) ns * n * sizeof(int16_t);
+        dev_in = c->stage[b];
+        dev_stride = n;
+        // after the kernels below
+        const bool invert = c->cfg.flags & M17B_INVERT;
+        ev_begin(c, c->compute, CAT_FIR, p);
+        launch_fir(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->head, c->cfg.flags & M17B_FIR_FMA, invert, c->compute);
+        ev_end(c, c->compute, p);
+        ev_begin(c, c->compute, CAT_AUX, p);
+        launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], c->compute);
+        ev_end(c, c->compute, p);
+        CK(cudaEventRecord(c->stage_free[b], c->compute));
+    } else {
+        const bool invert = c->cfg.flags & M17B_INVERT;
+        ev_begin(c, c->compute, CAT_FIR, p);
+        launch_fir(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->head, c->cfg.flags & M17B_FIR_FMA, invert, c->compute);
+        ev_end(c, c->compute, p);
+        ev_begin(c, c->compute, CAT_AUX, p);
+        launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], c->compute);
+        ev_end(c, c->compute, p);
+    }
+    CK(cudaGetLastError());
+    c->cur_tail ^= 1;
+    c->prof.fir_launches += 1;
+    c->prof.aux_launches += 1;
+    {
+        uint32_t b0 = c->head & ~7u;
+        uint32_t span = c->head + (uint32_t) n - b0;
+        c->prof.fir_samples += (uint64_t) c->d.np * (((span + 127) / 128) * 128);
+    }
+    c->head += (uint32_t) n;
+    c->head64 += n;
+    c->prof.scan_samples += (uint64_t) ns * n;
+
+    const int rounds = (int) (n / kMinFrameSpacing) + 2;
+    for (int r = 0; r != rounds; ++r) {
+        int rc = run_round(c);
+        if (rc != M17B_OK) return rc;
+    }
+    return M17B_OK;
+}
+
+int m17b_sync(m17b_ctx* c)
+{
+    if (!c) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = fetch_counters(c);
+    if (rc != M17B_OK) return rc;
+    for (int extra = 0; c->host_ctr.lagging != 0; ++extra) {
+        if (extra == 256) { c->last_error = "streams failed to reach the head"; return M17B_ESTATE; }
+        if ((rc = run_round(c)) != M17B_OK) return rc;
+        if ((rc = fetch_counters(c)) != M17B_OK) return rc;
+    }
+    ev_collect(c);
+    if (c->host_ctr.dropped) return M17B_EOVERFLOW;
+    return M17B_OK;
+}
+
+int m17b_pending_frames(m17b_ctx* c, size_t* n)
+{
+    if (!c || !n) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    *n = c->ready.size() + std::min(c->host_ctr.rec_count, c->d.rec_cap);
+    return rc;
+}
+
+int m17b_drain(m17b_ctx* c, m17b_frame* out, size_t cap, size_t* n)
+{
+    if (!c || !n || (!out && cap)) return M17B_EINVAL;
+    *n = 0;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    int rc2 = pull_records(c);
+    if (rc2 != M17B_OK) return rc2;
+    size_t k = std::min(cap, c->ready.size());
+    std::copy(c->ready.begin(), c->ready.begin() + (std::ptrdiff_t) k, out);
+    c->ready.erase(c->ready.begin(), c->ready.begin() + (std::ptrdiff_t) k);
+    *n = k;
+    c->prof.decode_frames += k;
+    return rc;
+}
+
+int m17b_diag_get(m17b_ctx* c, uint32_t stream, m17b_diag* out)
+{
+    if (!c || !out || stream >= c->cfg.n_streams) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    uint32_t f[NFIELDS];
+    CK(cudaMemcpy2D(f, sizeof(uint32_t), c->d.st + st_index(stream, 0), 32 * sizeof(uint32_t), sizeof(uint32_t),
+                    NFIELDS, cudaMemcpyDeviceToHost));
+    auto asf = [&](int i) { float v; std::memcpy(&v, &f[i], 4); return v; };
+    uint32_t fl = f[F_FLAGS];
+    // arguments of diagnostic_callback at M17Demodulator.h:746-750
+    out->dcd = (fl & FL_DCD) ? 1 : 0;
+    out->evm = std::sqrt(asf(F_EVM));                                     // SymbolEvm::evm(), StandardDeviation.h:79-82
+    out->deviation = 2400.f / asf(F_IDEV);                                // FreqDevEstimator.h:52
+    out->offset = asf(F_OFFSET);
+    out->locked = ((fl >> FL_STATE_SHIFT) & 7) != ST_UNLOCKED;
+    out->clock = asf(F_CK_EST);
+    out->sample_index = (int) ((fl >> FL_SI_SHIFT) & 15);
+    out->sync_index = (int) ((fl >> FL_SSI_SHIFT) & 15);
+    out->clock_index = (int) ((fl >> FL_CSI_SHIFT) & 15);
+    out->viterbi_cost = (int) f[F_VCOST];
+    out->samples = c->head64 - (uint64_t) (c->head - f[F_POS]);
+    return M17B_OK;
+}
+
+int m17b_counters_get(m17b_ctx* c, m17b_counters* out)
+{
+    if (!c || !out) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    out->samples = c->head64 * c->cfg.n_streams;
+    for (int i = 0; i != 6; ++i) out->frames[i] = c->host_ctr.frames[i];
+    out->lsf_crc_fail = c->host_ctr.lsf_crc_fail;
+    out->golay_fail = c->host_ctr.golay_fail;
+    out->faults = c->host_ctr.faults;
+    out->dropped = c->host_ctr.dropped;
+    return M17B_OK;
+}
+
+int m17b_get_profile(m17b_ctx* c, m17b_profile* out, int reset)
+{
+    if (!c || !out) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    *out = c->prof;
+    if (reset) c->prof = m17b_profile{};
+    return M17B_OK;
+}
+
+int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t stride, float* filtered_host,
+                      float* scaled_host)
+{
+    if (!c || !samples_host || !filtered_host || n == 0 || stride < n) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t ns = c->cfg.n_streams;
+    DevPtrs t{};
+    t.n_streams = ns;
+    t.np = c->d.np;
+    t.ring_chunks = next_pow2((uint32_t) ((n + 7) / 8 + 1));
+    size_t ring_bytes = (size_t) t.ring_chunks * t.np * 8 * sizeof(float);
+    int16_t *din = nullptr, *dtail = nullptr;
+    float *dy = nullptr, *dx = nullptr;
+    int rc = [&]() -> int {
+        CK(cudaMalloc(&t.ring_y, ring_bytes));
+        CK(cudaMalloc(&t.ring_x, ring_bytes));
+        CK(cudaMalloc(&din, (size_t) ns * n * sizeof(int16_t)));
+        CK(cudaMalloc(&dtail, (size_t) ns * kTailLen * sizeof(int16_t)));
+        CK(cudaMalloc(&dy, (size_t) ns * n * sizeof(float)));
+        CK(cudaMalloc(&dx, (size_t) ns * n * sizeof(float)));
+        CK(cudaMemsetAsync(dtail, 0, (size_t) ns * kTailLen * sizeof(int16_t), c->compute));
+        CK(cudaMemcpy2DAsync(din, n * sizeof(int16_t), samples_host, stride * sizeof(int16_t), n * sizeof(int16_t), ns,
+                             cudaMemcpyHostToDevice, c->compute));
+        launch_fir(t, din, n, (uint32_t) n, dtail, 0, c->cfg.flags & M17B_FIR_FMA, c->cfg.flags & M17B_INVERT, c->compute);
+        launch_gather(t, (uint32_t) n, dy, dx, c->compute);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(filtered_host, dy, (size_t) ns * n * sizeof(float), cudaMemcpyDeviceToHost, c->compute));
+        if (scaled_host)
+            CK(cudaMemcpyAsync(scaled_host, dx, (size_t) ns * n * sizeof(float), cudaMemcpyDeviceToHost, c->compute));
+        CK(cudaStreamSynchronize(c->compute));
+        return M17B_OK;
+    }();
+    cudaFree(t.ring_y); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx);
+    return rc;
+}
+
+int m17b_measure_fp32_peak(m17b_ctx* c, int variant, double* tflops)
+{
+    if (!c || !tflops) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->compute));
+    double v = run_fp32_peak(variant, c->sm_count, c->compute);
+    if (v < 0) return fail(c, cudaGetLastError(), "fp32 peak kernel");
+    *tflops = v;
+    return M17B_OK;
+}
+
+} // extern "C"

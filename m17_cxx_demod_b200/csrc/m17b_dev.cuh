@@ -1,0 +1,138 @@
+// m17b_dev.cuh -- device-side layout shared by the kernels and the host context.
+//
+// Data layout in HBM (N = streams padded to a multiple of 128, "Np"):
+//
+//   sample ring   ring_y / ring_x : float [RC chunks][Np][8]
+//       chunk c of stream s holds samples 8c .. 8c+7 (32 B = one DRAM sector).
+//       ring_x = the scaled input (apps/m17-demod.cpp:489), ring_y = matched
+//       filter output computed speculatively for every sample.  A warp of 32
+//       consecutive streams reads/writes 1 KiB contiguous per chunk, and a lane
+//       that runs ahead of / behind its neighbours still moves whole sectors.
+//   per-stream scalars            : uint32 [Np/32][NFIELDS][32]   (one coalesced
+//       128 B line per field per warp)
+//   correlator ring               : float [80][Np]    (Correlator::buffer_)
+//   sync-word peak samples        : float [30][Np]    (SyncWord::samples_ x3)
+//   FIR history snapshot          : float [149][Np]   (taken when DCD gates the filter)
+//   soft-bit frame                : int16 [184][Np]   (M17Framer buffer, 2 LLRs per symbol)
+//   decoder bytes                 : uint8 [56][Np]    (output_buffer union[26] + lsf[30])
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "m17b.h"
+
+namespace m17b {
+
+constexpr int kTaps = 150;            // M17Demodulator.h:79-118 (tap 149 is 0.0)
+constexpr int kTapsUsed = 149;
+constexpr int kTailLen = 160;         // raw history kept between submits (>= 148 + 7)
+constexpr int kChunk = 8;             // samples per ring chunk
+constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:149: 48000/400)
+constexpr int kRoundCap = 2048;       // samples a stream may advance per scan launch
+constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
+
+enum Field : int {
+    F_POS = 0,
+    F_RE0, F_IM0, F_RE1, F_IM1, F_L1, F_L2, F_LEVEL,
+    F_IIR0, F_IIR1, F_LIMIT,
+    F_CNT,          // count_ (low 16) | initializing (high 16)
+    F_IDX,          // corr_pos (8) | framer_index (16) << 8 | gap_k (8) << 24
+    F_FLAGS,
+    F_SW,           // SyncWord timing_index/triggered/updated x3
+    F_SYNC_COUNT, F_MISSING, F_VCOST,
+    F_CK_COUNT, F_CK_EST, F_CK_SEST,
+    F_CK_X0, F_CK_X1, F_CK_P00, F_CK_P01, F_CK_P10, F_CK_P11,
+    F_DMIN_X0, F_DMIN_X1, F_DMIN_P00, F_DMIN_P01, F_DMIN_P10, F_DMIN_P11,
+    F_DMAX_X0, F_DMAX_X1, F_DMAX_P00, F_DMAX_P01, F_DMAX_P10, F_DMAX_P11,
+    F_IDEV, F_OFFSET, F_EVM,
+    F_DEC,          // dec_state (8) | lich_segments (8) << 8 | depunct401 (8) << 16
+    F_SEQ,
+    NFIELDS
+};
+
+// F_FLAGS bit layout
+constexpr uint32_t FL_STATE_SHIFT = 0;    // 3 bits, DemodState; 7 = decided by the decode kernel
+constexpr uint32_t FL_SWT_SHIFT = 3;      // 2 bits, SyncWordType
+constexpr uint32_t FL_SI_SHIFT = 5;       // 4 bits, sample_index
+constexpr uint32_t FL_SSI_SHIFT = 9;      // 4 bits, sync_sample_index
+constexpr uint32_t FL_CSI_SHIFT = 13;     // 4 bits, clock_recovery.sample_index_
+constexpr uint32_t FL_DCD = 1u << 17;
+constexpr uint32_t FL_DCD_TRIG = 1u << 18;
+constexpr uint32_t FL_NEED_RESET = 1u << 19;
+constexpr uint32_t FL_NEED_UPDATE = 1u << 20;
+constexpr uint32_t FL_DEV_RESET = 1u << 21;
+constexpr uint32_t FL_EOT = 1u << 22;
+constexpr uint32_t FL_PENDING = 1u << 23;
+
+enum DemodState : int { ST_UNLOCKED, ST_LSF_SYNC, ST_STREAM_SYNC, ST_PACKET_SYNC, ST_BERT_SYNC, ST_SYNC_WAIT, ST_FRAME, ST_TBD };
+enum DecState : int { DEC_LSF, DEC_STREAM, DEC_BASIC_PACKET, DEC_FULL_PACKET, DEC_BERT };
+enum SyncType : int { SW_LSF, SW_STREAM, SW_PACKET, SW_BERT };
+
+struct Counters {                 // device-side mirror of m17b_counters (+ record ring cursor)
+    unsigned long long frames[6];
+    unsigned long long lsf_crc_fail;
+    unsigned long long golay_fail;
+    unsigned long long faults;
+    unsigned long long dropped;
+    unsigned int rec_count;       // records in the ring
+    unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
+};
+
+struct DevPtrs {
+    uint32_t* st;                 // [Np/32][NFIELDS][32]
+    float* ring_y;                // [RC][Np][8]
+    float* ring_x;
+    float* corr_ring;             // [80][Np]
+    float* sw_samples;            // [30][Np]
+    float* fir_snap;              // [149][Np]
+    int16_t* llr;                 // [184][Np]
+    uint8_t* dec_bytes;           // [56][Np]
+    m17b_frame* recs;             // [rec_cap]
+    Counters* ctr;
+    uint32_t n_streams;
+    uint32_t np;                  // padded stream count (multiple of 128)
+    uint32_t ring_chunks;         // RC, power of two
+    uint32_t rec_cap;
+};
+
+__host__ __device__ inline size_t st_index(uint32_t s, int f)
+{
+    return (size_t) (s >> 5) * (NFIELDS * 32) + (size_t) f * 32 + (s & 31);
+}
+
+// Viterbi input maps: one int16 per depunctured soft bit.  0 = erasure,
+// +-(k+1) = +-frame[k] (derandomise sign folded in, deinterleave folded in),
+// kMapStale = the stale depuncture_buffer element a BERT frame inherits.
+constexpr int16_t kMapStale = 0x7FFF;
+// kind: 0 LSF, 1 stream, 2 packet, 3 BERT (M17FrameDecoder.h:79-91)
+__host__ __device__ constexpr int map_len(int kind) { return kind == 0 ? 488 : kind == 1 ? 296 : kind == 2 ? 420 : 402; }
+__host__ __device__ constexpr int out_bits(int kind) { return kind == 0 ? 240 : kind == 1 ? 144 : kind == 2 ? 206 : 197; }
+
+struct ConstTables {
+    float taps[kTaps];
+    float sdft[4];                // re0, im0, re1, im1
+    float llr_thr[43];
+    int8_t llr_val[43][2];
+    int16_t vmap[4][488];
+    int16_t lichmap[96];          // LICH soft bits 0..95 of the deinterleaved frame
+    uint16_t crc_init;
+};
+
+// host side (m17b_tables.cpp)
+void build_tables(ConstTables& t, uint32_t* golay2048);
+
+// launchers (m17b_kernels.cu)
+cudaError_t upload_tables(const ConstTables& t, const uint32_t* golay2048);
+void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail,
+                uint32_t head, bool fma, bool invert, cudaStream_t s);
+void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
+                 int16_t* tail_out, cudaStream_t s);
+void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s);
+void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
+void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);
+void launch_init_state(const DevPtrs& d, cudaStream_t s);
+cudaError_t configure_kernels();
+double run_fp32_peak(int variant, int sm_count, cudaStream_t s);
+
+} // namespace m17b
