@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py -- M17 baseband Msamples/s demodulated on N B200 (driver contract).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = every channel of this rank advances by `chunk` samples (one m17b_submit of
+[channels][chunk] int16 + one drain of the decoded frame records).  Channels are continuous
+across steps (state stays resident on the GPU).  `value` times K steps with the inputs already
+in HBM; `e2e` times the same call sequence from pinned host memory, host->device copies and the
+device->host read of the frame records included.  Streams shard across ranks with no data-path
+collective (weak scaling: `channels` per GPU); only counters are gathered.
+
+--impl reference times the reference's own CPU implementation (oracle/_ref/m17-demod-ref, the
+unmodified reference headers, one forked process per stream over all host cores) on a bounded
+sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALG_FLOP_PER_SAMPLE = 300.0          # 150 multiplies + 150 adds per filtered sample
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4"])
+    ap.add_argument("--channels", type=int, default=0, help="channels per GPU (default: workload's)")
+    ap.add_argument("--chunk", type=int, default=9600, help="samples per channel per step")
+    ap.add_argument("--unique", type=int, default=1024, help="unique waveforms tiled over the channels")
+    ap.add_argument("--fma", action="store_true", help="fused multiply-add matched filter (not bit-identical)")
+    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--ref-streams", type=int, default=256, help="streams per step of the reference arm")
+    return ap.parse_args()
+
+
+def workload(args, total_samples):
+    from m17_cxx_demod_b200 import gen
+    seconds = total_samples / 48000.0
+    if args.workload == "c2":
+        w = gen.workload_c2(n_streams=args.unique, seconds=seconds)
+        channels = args.channels or 1024
+        desc = "configs[1]: stream-mode channels, AWGN Eb/N0 3-12 dB swept over channels"
+    elif args.workload == "c4":
+        w = gen.workload_c4(n_unique=args.unique, seconds=seconds)
+        channels = args.channels or 65536
+        desc = "configs[3]: mixed LSF/stream/packet/BERT traffic, SNR 15 dB"
+    else:
+        w = gen.workload_c3(n_unique=args.unique, seconds=seconds)
+        channels = args.channels or 65536
+        desc = "configs[2]: 65,536 channels, +-500 ppm clock skew, +-0.1 frequency offset, SNR 20 dB"
+    w.n_samples = total_samples
+    return w, channels, desc
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        busy = [v for v in sm if v > 0.5 * (mx or 1)] or sm
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def run_reference(args):
+    """The reference's CPU path on this box's host cores: rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    from m17_cxx_demod_b200 import gen
+    total = (args.steps + args.warmup) * args.chunk
+    w, channels, desc = workload(args, total)
+    cores = os.cpu_count() or 1
+    n_ref = min(args.ref_streams, len(w.params))
+    if not os.path.exists(ol.ref_binary()):
+        kind = "port"
+    else:
+        kind = "reference"
+    x = gen.generate(w.params[:n_ref], total)
+    times = []
+    records = 0
+    with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as td:
+        path = os.path.join(td, "x.s16")
+        x.tofile(path)
+        for step in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            if kind == "reference":
+                out = subprocess.run([ol.ref_binary(), "--batch", path, str(n_ref), str(total), "--jobs", str(cores), "--quiet"],
+                                     capture_output=True, text=True, check=True)
+                info = json.loads(out.stderr.strip().splitlines()[-1])
+                dt = info["seconds"]; records = info["records"]
+            else:
+                rec, _ = ol.demod_batch("port", x)
+                dt = time.perf_counter() - t0; records = sum(len(r) for r in rec)
+            if step >= args.warmup:
+                times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    value = n_ref * total / (ms * 1e-3) / 1e6
+    sample = f"{n_ref} of the workload's channels x {total} samples each per step, one forked m17-demod-ref process per stream, {cores} in flight"
+    line = {
+        "impl": "reference", "metric": "baseband_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "channels_per_gpu": channels, "chunk_samples": args.chunk, "unique_waveforms": len(w.params)},
+        "frames_per_s": records / (ms * 1e-3),
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import m17_cxx_demod_b200 as m
+    from m17_cxx_demod_b200 import gen
+    from m17_cxx_demod_b200.shard import shard_range, gather_counters
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    K, W, T = args.steps, args.warmup, args.chunk
+    total = (K + W) * T
+    w, channels, desc = workload(args, total)
+    U = len(w.params)
+    lo, hi = shard_range(channels * world, world, rank)       # weak scaling: `channels` per GPU
+    assert hi - lo == channels
+
+    # ---- synthetic input: U unique waveforms generated on the CPU, tiled on the device -------
+    t0 = time.perf_counter()
+    uniq = gen.generate(w.params, total)
+    gen_s = time.perf_counter() - t0
+    uniq_d = torch.from_numpy(uniq).to(dev)
+    idx = (torch.arange(lo, hi, device=dev) % U)
+    big = uniq_d.index_select(0, idx)                          # [channels][total] int16 resident in HBM
+    assert big.is_contiguous()
+    torch.cuda.synchronize()
+
+    flags = m.PROFILE | (m.FIR_FMA if args.fma else 0)
+    d = m.Demodulator(channels, T, flags=flags, device=local)
+    fp32_peak = d.measure_fp32_peak(1)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k):
+        d.submit_device(big.data_ptr() + 2 * k * T, T, total)
+        return d.drain()
+
+    n_frames = 0
+    records = []
+    for k in range(W):
+        records.append(step(k))
+    d.profile(reset=True)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    ev0.record()
+    d.event_record(0)
+    for k in range(W, W + K):
+        r = step(k)
+        n_frames += len(r)
+        records.append(r)
+    d.event_record(1)
+    ev1.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    t_dev = d.event_elapsed_ms(0, 1) * 1e-3      # CUDA events on the library's compute stream
+    clocks = sampler.stop()
+    prof = d.profile()
+    ctr = d.counters()
+    # Timed on the device (events on the launching stream); the host clock around the same K steps
+    # is reported beside it (m17b_drain() synchronises every step, so the two agree closely).
+    t = torch.tensor([t_dev], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t_max = float(t.item())
+    totals = gather_counters({"frames": n_frames, "samples": channels * K * T}, world, dev if world > 1 else None)
+
+    value = totals["samples"] / t_max / 1e6
+    fir_ms_per_launch = prof.fir_ms / max(1, prof.fir_launches)
+    fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
+    achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
+    kernel_ms = {"fir": prof.fir_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "aux": prof.aux_ms}
+    ksum = sum(kernel_ms.values()) or 1.0
+    launches = int(prof.fir_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches)
+
+    line = {
+        "metric": "baseband_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": 1e3 * t_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "channels_per_gpu": channels, "chunk_samples": T, "unique_waveforms": U,
+                   "filter": "fma" if args.fma else "exact (reference mul-then-add order, bit-identical)",
+                   "l2": f"inputs larger than L2 ({channels * T * 2 / 1e6:.0f} MB of int16 per step, never re-read)",
+                   "generator_s": round(gen_s, 2)},
+        "frames_per_s": totals["frames"] / t_max, "wall_s": t_wall, "device_s": t_dev,
+        "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
+                     "peak_source": "measured here: packed FFMA microkernel (m17b_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
+                     "alg_flop_per_sample": ALG_FLOP_PER_SAMPLE, "avg_launch_ms": fir_ms_per_launch},
+        "kernel_share": {k: v / ksum for k, v in kernel_ms.items()},
+        "kernel_ms_per_step": {k: v / K for k, v in kernel_ms.items()},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "frames_by_type": list(ctr.frames), "faults": int(ctr.faults), "dropped": int(ctr.dropped),
+    }
+
+    # ---- parity of the benchmarked run itself: every channel against the oracle of its waveform ----
+    if rank == 0 and not args.no_parity:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as ol
+        n_chk = min(U, 64)
+        want, _ = ol.demod_batch("ref" if ol.have_ref() else "port", uniq[:n_chk, :])
+        allrec = np.concatenate(records) if records else np.zeros(0, m.FRAME_DTYPE)
+        allrec = allrec[np.lexsort((allrec["seq"], allrec["stream"]))]
+        per = m.demod.split_by_stream(allrec, channels)
+        bad = 0
+        checked = 0
+        for s in range(channels):
+            u = (lo + s) % U
+            if u >= n_chk:
+                continue
+            checked += 1
+            if not ol.records_equal(want[u], per[s]):
+                bad += 1
+        line["parity"] = {"channels_checked": checked, "mismatching": bad, "oracle": "ref" if ol.have_ref() else "port"}
+
+    del d
+    # ---- e2e: same call sequence from pinned host memory --------------------------------------
+    if not args.no_e2e:
+        Ke = max(1, min(args.e2e_steps, K))
+        de = m.Demodulator(channels, T, flags=0, device=local)
+        bufs = [m.demod.PinnedBuffer((channels, T)) for _ in range(Ke + 1)]
+        idx_h = (np.arange(lo, hi) % U)
+        for k, b in enumerate(bufs):
+            np.take(uniq[:, k * T:(k + 1) * T], idx_h, axis=0, out=b.array)
+        de.submit(bufs[0].array)
+        de.drain()
+        barrier()
+        t0 = time.perf_counter()
+        d2h = 0
+        fr = 0
+        # submit k+1 is enqueued before the records of step k are read back, so the copy of the
+        # next chunk overlaps the kernels of the current one (double-buffered staging)
+        de.submit(bufs[1].array)
+        for k in range(1, Ke + 1):
+            if k + 1 <= Ke:
+                de.submit(bufs[k + 1].array)
+            r = de.drain()
+            d2h += r.nbytes
+            fr += len(r)
+        barrier()
+        te = time.perf_counter() - t0
+        tt = torch.tensor([te], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        te = float(tt.item())
+        line["e2e"] = {"value": world * channels * Ke * T / te / 1e6, "unit": "Msamples/s",
+                       "h2d_bytes_per_step": channels * T * 2, "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
+                       "frames_per_s": world * fr / te}
+        for b in bufs:
+            b.free()
+        del de
+
+    # ---- CPU baseline: the reference's own code on this box's host cores (rank 0, N = 1 only) ----
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as ol
+        cores = os.cpu_count() or 1
+        n_ref = min(U, 256)
+        with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as td:
+            path = os.path.join(td, "x.s16")
+            uniq[:n_ref].tofile(path)
+            if os.path.exists(ol.ref_binary()):
+                out = subprocess.run([ol.ref_binary(), "--batch", path, str(n_ref), str(total), "--jobs", str(cores), "--quiet"],
+                                     capture_output=True, text=True, check=True)
+                info = json.loads(out.stderr.strip().splitlines()[-1])
+                line["cpu_baseline"] = {"value": info["msamples_per_s"], "unit": "Msamples/s", "cores": cores, "kind": "reference",
+                                        "sample": f"{n_ref} channels x {total} samples, one m17-demod-ref process per stream, {cores} in flight, {info['seconds']:.2f} s wall"}
+            else:
+                t0 = time.perf_counter()
+                ol.demod_batch("port", uniq[:n_ref])
+                dt = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": n_ref * total / dt / 1e6, "unit": "Msamples/s", "cores": 1, "kind": "port",
+                                        "sample": f"{n_ref} channels x {total} samples, scalar port, {dt:.2f} s wall"}
+
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -171,6 +171,11 @@ int  m17b_diag_get(m17b_ctx* ctx, uint32_t stream, m17b_diag* out);
 int  m17b_counters_get(m17b_ctx* ctx, m17b_counters* out);
 int  m17b_get_profile(m17b_ctx* ctx, m17b_profile* out, int reset);
 
+/* Device-side timing for benchmarks: record CUDA event `slot` (0..7) on the context's compute
+ * stream now; elapsed milliseconds between two recorded slots (synchronises on `b`). */
+int  m17b_event_record(m17b_ctx* ctx, int slot);
+int  m17b_event_elapsed(m17b_ctx* ctx, int a, int b, double* ms);
+
 /* Kernel-level taps for parity tests: run ONLY the matched filter over
  * [n_streams][n] int16 (zero history) and return the n filtered floats per stream,
  * in the filter mode the context was created with. */

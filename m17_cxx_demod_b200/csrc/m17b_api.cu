@@ -45,6 +45,7 @@ struct m17b_ctx {
     std::vector<EvPair> ev_live, ev_pool;
     m17b_profile prof{};
     Counters host_ctr{};
+    cudaEvent_t marks[8] = {};
 };
 
 namespace {
@@ -158,6 +159,7 @@ void free_all(m17b_ctx* c)
     if (c->copy) cudaStreamSynchronize(c->copy);
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto& e : c->marks) if (e) cudaEventDestroy(e);
     cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
@@ -455,6 +457,26 @@ int m17b_get_profile(m17b_ctx* c, m17b_profile* out, int reset)
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
     *out = c->prof;
     if (reset) c->prof = m17b_profile{};
+    return M17B_OK;
+}
+
+int m17b_event_record(m17b_ctx* c, int slot)
+{
+    if (!c || slot < 0 || slot >= 8) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    if (!c->marks[slot]) CK(cudaEventCreate(&c->marks[slot]));
+    CK(cudaEventRecord(c->marks[slot], c->compute));
+    return M17B_OK;
+}
+
+int m17b_event_elapsed(m17b_ctx* c, int a, int b, double* ms)
+{
+    if (!c || !ms || a < 0 || a >= 8 || b < 0 || b >= 8 || !c->marks[a] || !c->marks[b]) return M17B_EINVAL;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaEventSynchronize(c->marks[b]));
+    float f = 0;
+    CK(cudaEventElapsedTime(&f, c->marks[a], c->marks[b]));
+    *ms = f;
     return M17B_OK;
 }
 

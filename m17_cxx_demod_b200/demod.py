@@ -72,7 +72,8 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_version.restype = ctypes.c_uint32
         for name in ("m17b_create", "m17b_submit", "m17b_sync", "m17b_drain", "m17b_pending_frames", "m17b_diag_get",
                      "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_measure_fp32_peak",
-                     "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count"):
+                     "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count",
+                     "m17b_event_record", "m17b_event_elapsed"):
             getattr(lib, name).restype = ctypes.c_int
         lib.m17b_submit.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int]
         lib.m17b_sync.argtypes = [ctypes.c_void_p]
@@ -92,6 +93,8 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_get_profile.argtypes = [ctypes.c_void_p, ctypes.POINTER(Profile), ctypes.c_int]
         lib.m17b_debug_filter.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
                                           ctypes.c_void_p, ctypes.c_void_p]
+        lib.m17b_event_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.m17b_event_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
         lib.m17b_measure_fp32_peak.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
         _lib = lib
     return _lib
@@ -232,6 +235,14 @@ class Demodulator:
     def measure_fp32_peak(self, variant: int = 0) -> float:
         v = ctypes.c_double()
         self._check(self._lib.m17b_measure_fp32_peak(self._ctx, variant, ctypes.byref(v)), "m17b_measure_fp32_peak")
+        return v.value
+
+    def event_record(self, slot: int):
+        self._check(self._lib.m17b_event_record(self._ctx, slot), "m17b_event_record")
+
+    def event_elapsed_ms(self, a: int, b: int) -> float:
+        v = ctypes.c_double()
+        self._check(self._lib.m17b_event_elapsed(self._ctx, a, b, ctypes.byref(v)), "m17b_event_elapsed")
         return v.value
 
     def device_alloc(self, nbytes: int) -> int:
