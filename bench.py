@@ -287,7 +287,6 @@ def main():
         n_chk = min(U, 64)
         want, _ = ol.demod_batch("ref" if ol.have_ref() else "port", uniq[:n_chk, :])
         allrec = np.concatenate(records) if records else np.zeros(0, m.FRAME_DTYPE)
-        allrec = allrec[np.lexsort((allrec["seq"], allrec["stream"]))]
         per = m.demod.split_by_stream(allrec, channels)
         bad = 0
         checked = 0

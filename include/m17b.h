@@ -73,7 +73,7 @@ typedef struct m17b_config {
     uint32_t max_chunk;        /* largest samples-per-stream a single m17b_submit may carry */
     uint32_t flags;            /* M17B_FIR_FMA | M17B_INVERT | M17B_PROFILE                */
     uint32_t frame_capacity;   /* frame records buffered on the device between drains
-                                  (0: n_streams * (max_chunk / 960 + 8))                   */
+                                  (0: n_streams * 2 * (max_chunk / 1600 + 2), the worst case)  */
     uint32_t reserved[3];
 } m17b_config;
 
@@ -160,8 +160,9 @@ int  m17b_submit(m17b_ctx* ctx, const int16_t* samples, size_t samples_per_strea
 /* Wait for all enqueued work; every stream has then consumed all submitted samples. */
 int  m17b_sync(m17b_ctx* ctx);
 
-/* m17b_sync(), then move up to `cap` frame records to `out`, ordered by (stream, seq).
- * *n receives the number written; call again while *n == cap. */
+/* m17b_sync(), then move up to `cap` frame records to `out`.  Records of one stream appear in
+ * chronological (seq) order; records of different streams are interleaved in the order the device
+ * completed them.  *n receives the number written; call again while *n == cap. */
 int  m17b_drain(m17b_ctx* ctx, m17b_frame* out, size_t cap, size_t* n);
 
 /* Number of frame records currently waiting on the device (after m17b_sync). */

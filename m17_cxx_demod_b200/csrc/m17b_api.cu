@@ -16,7 +16,6 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
-#include <deque>
 #include <new>
 #include <string>
 #include <vector>
@@ -38,8 +37,9 @@ struct m17b_ctx {
     unsigned long long head64 = 0;
     int sm_count = 0;
     std::string last_error;
-    // frame records pulled from the device, sorted, waiting for m17b_drain
-    std::deque<m17b_frame> ready;
+    // frame records pulled from the device (pinned), waiting for m17b_drain
+    m17b_frame* ready = nullptr;
+    size_t ready_n = 0, ready_off = 0, ready_cap = 0;
     // profiling
     bool profile = false;
     std::vector<EvPair> ev_live, ev_pool;
@@ -120,34 +120,31 @@ int fetch_counters(m17b_ctx* c)
     return M17B_OK;
 }
 
-// Pull every record off the device, order by (stream, seq), append to c->ready.
+// Move every record off the device into c->ready (pinned staging).  The device appends records
+// with one atomic counter, so records of one stream are already in chronological order.
 int pull_records(m17b_ctx* c)
 {
     uint32_t n = std::min(c->host_ctr.rec_count, c->d.rec_cap);
     if (n == 0) return M17B_OK;
-    std::vector<m17b_frame> tmp(n);
+    if (c->ready_off == c->ready_n) c->ready_off = c->ready_n = 0;
+    if (c->ready_n + n > c->ready_cap) {
+        size_t cap = std::max<size_t>((c->ready_n + n) * 2, 4096);
+        m17b_frame* nb = nullptr;
+        CK(cudaHostAlloc((void**) &nb, cap * sizeof(m17b_frame), cudaHostAllocDefault));
+        if (c->ready_n) std::memcpy(nb, c->ready, c->ready_n * sizeof(m17b_frame));
+        if (c->ready) cudaFreeHost(c->ready);
+        c->ready = nb;
+        c->ready_cap = cap;
+    }
     EvPair p{};
     ev_begin(c, c->compute, CAT_D2H, p);
-    CK(cudaMemcpyAsync(tmp.data(), c->d.recs, sizeof(m17b_frame) * n, cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaMemcpyAsync(c->ready + c->ready_n, c->d.recs, sizeof(m17b_frame) * n, cudaMemcpyDeviceToHost, c->compute));
     ev_end(c, c->compute, p);
     CK(cudaMemsetAsync(&c->d.ctr->rec_count, 0, sizeof(unsigned int), c->compute));
     CK(cudaStreamSynchronize(c->compute));
     c->prof.d2h_bytes += sizeof(m17b_frame) * n;
     c->host_ctr.rec_count = 0;
-    std::sort(tmp.begin(), tmp.end(), [](const m17b_frame& a, const m17b_frame& b) {
-        return a.stream != b.stream ? a.stream < b.stream : a.seq < b.seq;
-    });
-    // merge with what is already waiting (older records of a stream come first)
-    if (c->ready.empty()) {
-        c->ready.assign(tmp.begin(), tmp.end());
-    } else {
-        std::vector<m17b_frame> merged(c->ready.size() + tmp.size());
-        std::merge(c->ready.begin(), c->ready.end(), tmp.begin(), tmp.end(), merged.begin(),
-                   [](const m17b_frame& a, const m17b_frame& b) {
-                       return a.stream != b.stream ? a.stream < b.stream : a.seq < b.seq;
-                   });
-        c->ready.assign(merged.begin(), merged.end());
-    }
+    c->ready_n += n;
     return M17B_OK;
 }
 
@@ -163,6 +160,7 @@ void free_all(m17b_ctx* c)
     cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
+    if (c->ready) cudaFreeHost(c->ready);
     for (int i = 0; i != 2; ++i) {
         cudaFree(c->tail[i]); cudaFree(c->stage[i]);
         if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
@@ -227,8 +225,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         // of the slow filter path / sliding DFT
         uint32_t need = cfg->max_chunk + kRoundCap + 160 + 16;
         d.ring_chunks = next_pow2((need + 7) / 8);
+        // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
         d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
-                                        : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * (cfg->max_chunk / 960 + 8), 0x7fffffffull);
+                                        : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 2 * (cfg->max_chunk / kMinFrameSpacing + 2), 0x7fffffffull);
         size_t np = d.np;
         size_t ring_bytes = (size_t) d.ring_chunks * np * 8 * sizeof(float);
         CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
@@ -391,7 +390,7 @@ int m17b_pending_frames(m17b_ctx* c, size_t* n)
     if (!c || !n) return M17B_EINVAL;
     int rc = m17b_sync(c);
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
-    *n = c->ready.size() + std::min(c->host_ctr.rec_count, c->d.rec_cap);
+    *n = (c->ready_n - c->ready_off) + std::min(c->host_ctr.rec_count, c->d.rec_cap);
     return rc;
 }
 
@@ -403,9 +402,9 @@ int m17b_drain(m17b_ctx* c, m17b_frame* out, size_t cap, size_t* n)
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
     int rc2 = pull_records(c);
     if (rc2 != M17B_OK) return rc2;
-    size_t k = std::min(cap, c->ready.size());
-    std::copy(c->ready.begin(), c->ready.begin() + (std::ptrdiff_t) k, out);
-    c->ready.erase(c->ready.begin(), c->ready.begin() + (std::ptrdiff_t) k);
+    size_t k = std::min(cap, c->ready_n - c->ready_off);
+    if (k) std::memcpy(out, c->ready + c->ready_off, k * sizeof(m17b_frame));
+    c->ready_off += k;
     *n = k;
     c->prof.decode_frames += k;
     return rc;

@@ -433,19 +433,22 @@ __device__ __noinline__ float slow_fir(const float* snap, const float* ring_x, u
     return result;
 }
 
-// Util.h:128-145 (llr<float,4>) -> packed (second << 8 | first) int8 pair
-__device__ __forceinline__ uint32_t llr4(float sample)
+// Util.h:128-145 (llr<float,4>) -> packed (second << 8 | first) int8 pair.  The reference
+// binary-searches 43 thresholds spaced ~1/7 apart; the same lower_bound index is found here
+// from an arithmetic first guess corrected against the thresholds themselves (a copy of the
+// table in shared memory: lanes look up different entries).
+struct LlrTable { float thr[44]; uint32_t val[44]; };
+
+__device__ __forceinline__ uint32_t llr4(const LlrTable& tab, float sample)
 {
     float t = (-3.0f < sample) ? sample : -3.0f;      // std::max(MIN_VALUE, sample)
     float v = (t < 3.0f) ? t : 3.0f;                  // std::min(MAX_VALUE, t)
-    int lo = 0, len = 43;                             // std::lower_bound
-    while (len > 0) {
-        int half = len >> 1;
-        if (c_tab.llr_thr[lo + half] < v) { lo = lo + half + 1; len = len - half - 1; }
-        else len = half;
-    }
-    if (lo == 43) lo = 42;
-    return (uint32_t) (uint8_t) c_tab.llr_val[lo][0] | ((uint32_t) (uint8_t) c_tab.llr_val[lo][1] << 8);
+    int g = (int) ((v + 3.0f) * 7.0f);                // about the number of thresholds below v
+    g = g < 0 ? 0 : (g > 43 ? 43 : g);
+    while (g > 0 && !(tab.thr[g - 1] < v)) --g;       // lower_bound: first index with !(thr < v)
+    while (g < 43 && tab.thr[g] < v) ++g;
+    if (g == 43) g = 42;
+    return tab.val[g];
 }
 
 // Per-thread working set of the scan; only ever touched by inlined code.
@@ -464,7 +467,10 @@ struct Scan {
     uint32_t sw;                               // packed SyncWord state, 8 bits per word
 };
 
+constexpr size_t kScanSmem = sizeof(float) * (80 + 24) * kScanThreads + sizeof(LlrTable);
+
 struct ScanEnv {
+    const LlrTable* llr_tab;
     uint32_t* sb;          // &st[block][0][lane]
     float* ring;           // smem column
     float* sw_samples;     // + s
@@ -673,7 +679,13 @@ __device__ __forceinline__ void do_frame(Scan& z, const ScanEnv& e, float filter
     int diff = z.si - idx;
     if (diff == 5 || diff == -5) {
         // ClockRecovery.h:76-88
-        double csw = fmod((double) (z.ck_sest + z.ck_est * (float) z.ck_count), 10.0);
+        // fmod(v, 10) is v itself for |v| < 10 and v -+ 10 (exact) for |v| < 20; libm otherwise
+        const float v = z.ck_sest + z.ck_est * (float) z.ck_count;
+        const float av = fabsf(v);
+        double csw;
+        if (av < 10.f) csw = (double) v;
+        else if (av < 20.f) csw = (double) v - (v < 0 ? -10.0 : 10.0);
+        else csw = fmod((double) v, 10.0);
         if (csw < 0.) csw += 10;
         else if (csw >= 10) csw -= 10;
         z.csi = wrap_index((int) (int8_t) round(csw));
@@ -694,7 +706,7 @@ __device__ __forceinline__ void do_frame(Scan& z, const ScanEnv& e, float filter
     z.evm -= z.evm * alpha;
     z.evm += (err * err) * alpha;
 
-    uint32_t pair = llr4(sample);
+    uint32_t pair = llr4(*e.llr_tab, sample);
     e.llr[(size_t) (z.framer_index >> 1) * e.np] = (int16_t) pair;      // M17Framer.h:42-53
     z.framer_index += 2;
     if (z.framer_index != 368) return;
@@ -710,11 +722,18 @@ scan_kernel(DevPtrs d, uint32_t head)
     extern __shared__ float smem[];
     float* ring_s = smem;                                  // [80][128]
     float* stage = smem + 80 * kScanThreads;               // [3][8][128]
+    LlrTable* tab = reinterpret_cast<LlrTable*>(smem + (80 + 24) * kScanThreads);
     const int tid = threadIdx.x;
+    if (tid < 43) {
+        tab->thr[tid] = c_tab.llr_thr[tid];
+        tab->val[tid] = (uint32_t) (uint8_t) c_tab.llr_val[tid][0] | ((uint32_t) (uint8_t) c_tab.llr_val[tid][1] << 8);
+    }
+    __syncthreads();
     const uint32_t s = blockIdx.x * kScanThreads + tid;
     if (s >= d.n_streams) return;
 
     ScanEnv e;
+    e.llr_tab = tab;
     e.sb = d.st + st_index(s, 0);
     e.ring = ring_s + tid;
     e.sw_samples = d.sw_samples + s;
@@ -801,7 +820,7 @@ scan_kernel(DevPtrs d, uint32_t head)
                 --z.init;
                 filtered = y_spec;              // the filter has run on every sample since sample 0
             } else if (!z.dcd) {                // :675-689
-                if (z.count % 384 == 0) {
+                if (z.count % 384 == 0) {   // count_ in [1, 384] here
                     update_dcd(z, e);
                     dcd_update(z);
                     z.count = 0;
@@ -919,7 +938,7 @@ scan_kernel(DevPtrs d, uint32_t head)
 
 void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s)
 {
-    size_t smem = sizeof(float) * (80 + 24) * kScanThreads;
+    size_t smem = kScanSmem;
     scan_kernel<<<d.np / kScanThreads, kScanThreads, smem, s>>>(d, head);
 }
 
@@ -1193,8 +1212,7 @@ void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, c
 // Per-device kernel attributes (dynamic shared memory above 48 KiB).
 cudaError_t configure_kernels()
 {
-    cudaError_t e = cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int) (sizeof(float) * (80 + 24) * kScanThreads));
+    cudaError_t e = cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kScanSmem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int) (sizeof(uint16_t) * 244 * kDecThreads));

@@ -186,7 +186,7 @@ class Demodulator:
         self._keep.clear()
 
     def drain(self) -> np.ndarray:
-        """All frame records decoded so far, ordered by (stream, seq)."""
+        """All frame records decoded so far (chronological within each stream)."""
         self.sync()
         n = ctypes.c_size_t()
         self._check(self._lib.m17b_pending_frames(self._ctx, ctypes.byref(n)), "m17b_pending_frames")
@@ -200,9 +200,11 @@ class Demodulator:
         """Feed [n_streams, n] int16 in chunks; return per-stream record arrays."""
         n = samples.shape[1]
         chunk = min(chunk or self.max_chunk, self.max_chunk)
+        parts = []
         for o in range(0, n, chunk):
             self.submit(samples[:, o:o + chunk])
-        rec = self.drain()
+            parts.append(self.drain())
+        rec = np.concatenate(parts) if parts else np.zeros(0, FRAME_DTYPE)
         return split_by_stream(rec, self.n_streams)
 
     def diag(self, stream: int) -> Diag:
@@ -260,6 +262,7 @@ class Demodulator:
 
 
 def split_by_stream(rec: np.ndarray, n_streams: int) -> list[np.ndarray]:
-    """rec is sorted by (stream, seq); return one array per stream."""
+    """Group records by stream (stable: keeps each stream's chronological order)."""
+    rec = rec[np.lexsort((rec["seq"], rec["stream"]))]
     idx = np.searchsorted(rec["stream"], np.arange(n_streams + 1))
     return [rec[idx[s]:idx[s + 1]] for s in range(n_streams)]

@@ -96,12 +96,15 @@ def test_chunking_does_not_change_results():
     want, _ = ol.demod_batch("port", x)
     sizes = [1, 7, 8, 13, 1919, 1920, 1921, 4800, 5003]
     with m.Demodulator(33, 6000) as d:
-        o, k = 0, 0
+        o, k, parts = 0, 0, []
         while o < x.shape[1]:
             n = min(sizes[k % len(sizes)], x.shape[1] - o)
             d.submit(np.ascontiguousarray(x[:, o:o + n]))
+            if k % 5 == 4:
+                parts.append(d.drain())
             o += n; k += 1
-        got = m.demod.split_by_stream(d.drain(), 33)
+        parts.append(d.drain())
+        got = m.demod.split_by_stream(np.concatenate(parts), 33)
     assert_records_match(want, got, "ragged")
 
 
