@@ -157,7 +157,7 @@ void free_all(m17b_ctx* c)
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -233,7 +233,8 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
         CK(cudaMalloc(&d.ring_y, ring_bytes));
         CK(cudaMalloc(&d.ring_x, ring_bytes));
-        CK(cudaMalloc(&d.corr_ring, 80 * np * sizeof(float)));
+        CK(cudaMalloc(&d.corr_ring, 96 * np * sizeof(float)));
+        CK(cudaMalloc(&d.lim_save, 8 * np * sizeof(float)));
         CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
         CK(cudaMalloc(&d.fir_snap, (size_t) kTapsUsed * np * sizeof(float)));
         CK(cudaMalloc(&d.llr, 184 * np * sizeof(int16_t)));
@@ -242,7 +243,8 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.ctr, sizeof(Counters)));
         CK(cudaMemsetAsync(d.ring_y, 0, ring_bytes, c->compute));
         CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes, c->compute));
-        CK(cudaMemsetAsync(d.corr_ring, 0, 80 * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.corr_ring, 0, 96 * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.lim_save, 0, 8 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.sw_samples, 0, 30 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.fir_snap, 0, (size_t) kTapsUsed * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.llr, 0, 184 * np * sizeof(int16_t), c->compute));

@@ -10,7 +10,8 @@
 //       that runs ahead of / behind its neighbours still moves whole sectors.
 //   per-stream scalars            : uint32 [Np/32][NFIELDS][32]   (one coalesced
 //       128 B line per field per warp)
-//   correlator ring               : float [80][Np]    (Correlator::buffer_)
+//   correlator ring               : float [96][Np]    (Correlator::buffer_ + one block of look-ahead)
+//   limit look-ahead              : float [8][Np]     (limit_ of samples the dense pass ran ahead by)
 //   sync-word peak samples        : float [30][Np]    (SyncWord::samples_ x3)
 //   FIR history snapshot          : float [149][Np]   (taken when DCD gates the filter)
 //   soft-bit frame                : int16 [184][Np]   (M17Framer buffer, 2 LLRs per symbol)
@@ -48,6 +49,8 @@ enum Field : int {
     F_IDEV, F_OFFSET, F_EVM,
     F_DEC,          // dec_state (8) | lich_segments (8) << 8 | depunct401 (8) << 16
     F_SEQ,
+    F_DPOS,         // position of the dense pass (>= F_POS, same 8-sample block)
+    F_RP,           // next physical slot of the 96-entry correlator ring
     NFIELDS
 };
 
@@ -83,7 +86,8 @@ struct DevPtrs {
     uint32_t* st;                 // [Np/32][NFIELDS][32]
     float* ring_y;                // [RC][Np][8]
     float* ring_x;
-    float* corr_ring;             // [80][Np]
+    float* corr_ring;             // [96][Np]
+    float* lim_save;              // [8][Np]
     float* sw_samples;            // [30][Np]
     float* fir_snap;              // [149][Np]
     int16_t* llr;                 // [184][Np]

@@ -1,0 +1,1176 @@
+// m17b_lane.cuh -- the per-stream ("lane") logic of the scan and decode kernels.
+//
+// One lane = one M17 stream = one CUDA thread.  Everything here is straight-line
+// per-lane code with no warp intrinsics, so the very same source also compiles
+// with g++ as a single-lane host build (tests/emu/, test infrastructure only)
+// that replays the kernels' arithmetic on the CPU against the oracle.  Under nvcc
+// the functions are __device__ only: the product has no CPU path.
+//
+//   scan_lane()    M17Demodulator::operator()                M17Demodulator.h:656-753
+//   decode_lane()  M17FrameDecoder::operator()               M17FrameDecoder.h:353-392
+//
+// Structure of scan_lane (why it looks nothing like the reference's loop):
+// the reference does everything once per sample.  Only three things really are
+// per-sample recurrences: the two sliding-DFT bins of the carrier detect
+// (SlidingDFT.h:118-132), the correlator's limit biquad (Correlator.h:43-49) and
+// the correlator ring write.  The state machine around them acts on a few
+// samples per symbol at most.  A lane therefore walks its samples in aligned
+// blocks of 8 (one 32-byte sector of the sample ring) in two passes:
+//   dense pass   branch-free recurrences for the block's samples; the per-sample
+//                limit values go to a small shared-memory array;
+//   event pass   jumps from one sample the state machine can act on to the next
+//                (quiet_samples() gives the distance in closed form), running the
+//                reference's per-sample logic only there.
+// All lanes of a warp execute the dense pass together whatever state they are in;
+// the divergent part shrinks to the events.  The carrier-detect cadence (384 /
+// 960 samples) and the 1920-sample start-up are multiples of 8 from sample 0, so
+// mode changes (filter clocked or not) only ever happen at block ends.
+//
+// The dense pass may run ahead of the event pass inside one block (a lane stops
+// at the sample that completes a frame and waits for decode_kernel).  The
+// correlator ring therefore keeps 96 samples physically (the reference's 80 plus
+// a block of look-ahead) and is addressed relative to the sample being handled.
+#pragma once
+
+#include "m17b_dev.cuh"
+
+#include <math.h>
+#include <string.h>
+
+#ifdef __CUDACC__
+#define M17B_FN __device__ __forceinline__
+#define M17B_FN_COLD __device__ __noinline__
+#define M17B_TAB c_tab
+#define M17B_GOLAY g_golay
+#else
+#define M17B_FN inline
+#define M17B_FN_COLD inline
+#define M17B_TAB ::m17b::h_tab
+#define M17B_GOLAY ::m17b::h_golay
+#endif
+
+namespace m17b {
+
+#ifdef __CUDACC__
+constexpr int RS = 128;                 // shared-memory column stride == threads per CTA
+M17B_FN float u2f(uint32_t v) { return __uint_as_float(v); }
+M17B_FN uint32_t f2u(float v) { return __float_as_uint(v); }
+M17B_FN float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+M17B_FN float add_rn(float a, float b) { return __fadd_rn(a, b); }
+M17B_FN int popc(uint32_t v) { return __popc(v); }
+M17B_FN void ctr_add(unsigned long long* p, unsigned long long v) { atomicAdd(p, v); }
+M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { return atomicAdd(p, v); }
+#else
+constexpr int RS = 1;
+extern ConstTables h_tab;
+extern uint32_t h_golay[2048];
+M17B_FN float u2f(uint32_t v) { float f; memcpy(&f, &v, 4); return f; }
+M17B_FN uint32_t f2u(float f) { uint32_t v; memcpy(&v, &f, 4); return v; }
+M17B_FN float mul_rn(float a, float b) { return a * b; }     // built with -ffp-contract=off
+M17B_FN float add_rn(float a, float b) { return a + b; }
+M17B_FN int popc(uint32_t v) { return __builtin_popcount(v); }
+M17B_FN void ctr_add(unsigned long long* p, unsigned long long v) { *p += v; }
+M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { unsigned int o = *p; *p += v; return o; }
+#endif
+
+constexpr int kRing = 96;               // physical correlator ring (Correlator::buffer_ is 80)
+
+// ---------------------------------------------------------------------------
+// Kalman filters
+// ---------------------------------------------------------------------------
+
+struct Kalman { float x0, x1, p00, p01, p10, p11; };
+
+M17B_FN Kalman kf_load(const uint32_t* sb, int f)
+{
+    Kalman k;
+    k.x0 = u2f(sb[(f + 0) * 32]); k.x1 = u2f(sb[(f + 1) * 32]);
+    k.p00 = u2f(sb[(f + 2) * 32]); k.p01 = u2f(sb[(f + 3) * 32]);
+    k.p10 = u2f(sb[(f + 4) * 32]); k.p11 = u2f(sb[(f + 5) * 32]);
+    return k;
+}
+
+M17B_FN void kf_store(uint32_t* sb, int f, const Kalman& k)
+{
+    sb[(f + 0) * 32] = f2u(k.x0); sb[(f + 1) * 32] = f2u(k.x1);
+    sb[(f + 2) * 32] = f2u(k.p00); sb[(f + 3) * 32] = f2u(k.p01);
+    sb[(f + 4) * 32] = f2u(k.p10); sb[(f + 5) * 32] = f2u(k.p11);
+}
+
+// KalmanFilter.h:33-38 / :83-88
+M17B_FN void kf_reset(Kalman& k, float z)
+{
+    k.x0 = z; k.x1 = 0.f; k.p00 = 4.f; k.p01 = 0.f; k.p10 = 0.f; k.p11 = 0.00000025f;
+}
+
+// KalmanFilter.h:40-65 (wrap) / :90-107.  The reference evaluates this through
+// blaze expression templates; operation order and precision below are those of
+// the compiled reference (float 2-term sums; the gain scaled in double and
+// rounded to float before the state add; the covariance update in double).
+// The multiplications by H = [1 0] and F = [[1 dt][0 1]] entries are kept so
+// that NaN/Inf propagate identically.
+M17B_FN void kf_update(Kalman& k, float z, float dt, bool wrap)
+{
+    const float Q00 = 6.25e-13f, Q01 = 1.25e-12f, Q10 = 1.25e-12f, Q11 = 2.50e-12f, R = 0.5f;
+    const float one = 1.f, zero = 0.f;
+    float x0 = k.x0 * one + k.x1 * dt;
+    float x1 = k.x0 * zero + k.x1 * one;
+    float T00 = one * k.p00 + dt * k.p10;
+    float T01 = one * k.p01 + dt * k.p11;
+    float T10 = zero * k.p00 + one * k.p10;
+    float T11 = zero * k.p01 + one * k.p11;
+    float P00 = (one * T00 + dt * T01) + Q00;
+    float P01 = (zero * T00 + one * T01) + Q01;
+    float P10 = (one * T10 + dt * T11) + Q10;
+    float P11 = (zero * T10 + one * T11) + Q11;
+    float HP0 = one * P00 + zero * P10;
+    float HP1 = one * P01 + zero * P11;
+    float S = (HP0 * one + HP1 * zero) + R;
+    double sinv = 1.0 / (double) S;
+    if (wrap) {
+        if ((double) (z - x0) < -5.0) z += 10.f;
+        else if ((double) (z - x0) > 5.0) z -= 10.f;
+    }
+    float y = z - (x0 * one + x1 * zero);
+    float hy0 = y * one, hy1 = y * zero;
+    float k0 = hy0 * P00 + hy1 * P01;
+    float k1 = hy0 * P10 + hy1 * P11;
+    x0 = x0 + (float) ((double) k0 * sinv);
+    x1 = x1 + (float) ((double) k1 * sinv);
+    if (wrap) {
+        while (x0 >= 10.f) x0 -= 10.f;
+        while (x0 < 0) x0 += 10.f;
+    }
+    float a0 = P00 * one + P01 * zero;
+    float a1 = P10 * one + P11 * zero;
+    float a0h0 = a0 * one, a0h1 = a0 * zero, a1h0 = a1 * one, a1h1 = a1 * zero;
+    k.p00 = (float) ((double) P00 - ((double) (P00 * a0h0) + (double) (a0h1 * P10)) * sinv);
+    k.p01 = (float) ((double) P01 - ((double) (P01 * a0h0) + (double) (a0h1 * P11)) * sinv);
+    k.p10 = (float) ((double) P10 - ((double) (P00 * a1h0) + (double) (a1h1 * P10)) * sinv);
+    k.p11 = (float) ((double) P11 - ((double) (P01 * a1h0) + (double) (a1h1 * P11)) * sinv);
+    k.x0 = x0; k.x1 = x1;
+}
+
+M17B_FN int wrap_index(int v)      // ClockRecovery.h:61-62 on int8
+{
+    v = v < 0 ? v + 10 : v;
+    v = v >= 10 ? v - 10 : v;
+    return v;
+}
+
+// (int8_t) round(double(v)) for a float v in (-128, 128): round half away from zero.
+// trunc and the subtraction are exact in float, so no double arithmetic is needed.
+M17B_FN int round_half_away(float v)
+{
+    if (!(v == v)) return 0;            // NaN converts to 0 through the reference's int8_t cast
+    float t = truncf(v);
+    float fr = v - t;
+    int r = (int) t;
+    if (fr >= 0.5f) r += 1;
+    else if (fr <= -0.5f) r -= 1;
+    return r;
+}
+
+// ---------------------------------------------------------------------------
+// correlator ring access.  `ph` = physical slot of the sample being handled
+// (0..95); a sample clocked in d steps earlier sits at slot ph - d (mod 96).
+// ---------------------------------------------------------------------------
+
+M17B_FN float ring_back(const float* ring, int ph, int d)
+{
+    int p = ph - d;
+    p = p < 0 ? p + kRing : p;
+    return ring[p * RS];
+}
+
+// Correlator.h:51-64: sum over i of sync[i] * buffer_[(prev_pos + 10 (i + 1)) % 80],
+// i.e. the samples 70, 60, ..., 0 steps back, oldest first.
+M17B_FN float correlate(const float* ring, int ph, uint32_t word /* bit i: sync[i] = -3 */)
+{
+    float result = 0.f;
+#pragma unroll
+    for (int i = 0; i != 8; ++i) {
+        float sy = ((word >> i) & 1) ? -3.f : 3.f;
+        result = result + sy * ring_back(ring, ph, 70 - 10 * i);
+    }
+    return result;
+}
+
+// sync words, bit i set <=> symbol i is -3 (M17Demodulator.h:154-157)
+constexpr uint32_t kWordPreamble = 0xAA;   // +3,-3,+3,-3,+3,-3,+3,-3
+constexpr uint32_t kWordLsf = 0xB0;        // +3,+3,+3,+3,-3,-3,+3,-3
+constexpr uint32_t kWordPacket = 0xF2;     // +3,-3,+3,+3,-3,-3,-3,-3
+constexpr uint32_t kWordEot = 0x40;        // +3,+3,+3,+3,+3,+3,-3,+3
+constexpr float kLowest = -3.402823466e+38f;   // numeric_limits<float>::lowest(), Correlator.h:143
+
+// Correlator.h:150-157
+M17B_FN float sync_triggered(const float* ring, int ph, float limit, uint32_t word, float m1, float m2)
+{
+    float limit_1 = limit * m1;
+    float limit_2 = limit * m2;
+    float value = correlate(ring, ph, word);
+    return (value > limit_1 || value < limit_2) ? value : 0.0f;
+}
+
+// Correlator.h:161-207: SyncWord::operator() followed by updated().  `f` is the
+// packed {timing_index:4, triggered:1}; returns new f | (updated & 3) << 8
+// (updated: 0, 1, or 3 for -1).  samples = SyncWord::samples_ column, stride np.
+M17B_FN_COLD uint32_t sync_step(float* samples, size_t np, const float* ring, int ph, int idx10, float limit,
+                                uint32_t word, float m1, float m2, uint32_t f)
+{
+    float value = sync_triggered(ring, ph, limit, word, m1, m2);
+    uint32_t timing_index = f & 0xF;
+    bool trig = (f >> 4) & 1;
+    uint32_t updated = 0;
+    if (value != 0) {
+        if (!trig) {
+            for (int i = 0; i != 10; ++i) samples[(size_t) i * np] = 0.f;
+            trig = true;
+        }
+        samples[(size_t) idx10 * np] = value;
+    } else if (trig) {
+        trig = false;
+        timing_index = 0;
+        float peak = value;
+        for (int i = 0; i != 10; ++i) {
+            float v = samples[(size_t) i * np];
+            if (fabsf(v) > fabsf(peak)) { peak = v; timing_index = i; }
+        }
+        updated = peak > 0 ? 1u : 3u;
+    }
+    return timing_index | ((uint32_t) trig << 4) | (updated << 8);
+}
+
+// M17Demodulator.h:232-241: Correlator::outer_symbol_levels (Correlator.h:81-114,
+// incl. `avg = max + min / 2.`) + FreqDevEstimator::update (FreqDevEstimator.h:31-48).
+// pp = logical buffer position (0..79) of the sample being handled, ph its physical
+// slot.  Returns (offset, idev); dev.reset_ is always false afterwards.
+struct F2 { float x, y; };
+
+M17B_FN_COLD F2 update_values(uint32_t* sb, const float* ring, int si, int pp, int ph, bool dev_reset)
+{
+    float min_sum = 0, max_sum = 0;
+    int min_count = 0, max_count = 0;
+    float lv[8];
+    int n = 0;
+    for (int i = si; i < 80; i += 10) {
+        int d = pp - i;
+        d = d < 0 ? d + 80 : d;
+        lv[n++] = ring_back(ring, ph, d);
+    }
+    float min_level = lv[0], max_level = lv[0];
+    for (int i = 0; i != n; ++i) {
+        float v = lv[i];
+        min_level = v < min_level ? v : min_level;
+        max_level = max_level < v ? v : max_level;
+    }
+    float avg = (float) ((double) max_level + (double) min_level / 2.);
+    for (int i = 0; i != n; ++i) {
+        float v = lv[i];
+        bool high = v > avg, low = v < avg;
+        max_sum += v * (high ? 1.f : 0.f);
+        min_sum += v * (low ? 1.f : 0.f);
+        max_count += high;
+        min_count += low;
+    }
+    float minValue = min_count > 0 ? min_sum / (float) min_count : min_level;
+    float maxValue = max_count > 0 ? max_sum / (float) max_count : max_level;
+
+    Kalman mn = kf_load(sb, F_DMIN_X0), mx = kf_load(sb, F_DMAX_X0);
+    kf_update(mn, minValue, 192.f, false);
+    kf_update(mx, maxValue, 192.f, false);
+    float offset = (float) ((double) (mx.x0 + mn.x0) / 2.);
+    float idev = (float) (6.0 / (double) (mx.x0 - mn.x0));
+    if (isnan(mn.x0) || isnan(mn.x1) || isnan(mx.x0) || isnan(mx.x1)) dev_reset = true;
+    if (dev_reset) {
+        kf_reset(mn, minValue);
+        kf_reset(mx, maxValue);
+        offset = (minValue + maxValue) / 2.f;
+        idev = (float) (6.0 / (double) (maxValue - minValue));
+    }
+    kf_store(sb, F_DMIN_X0, mn);
+    kf_store(sb, F_DMAX_X0, mx);
+    F2 r; r.x = offset; r.y = idev;
+    return r;
+}
+
+// ClockRecovery.h:54-67: Kalman update with the sync word's index; returns
+// (sample_estimate_, clock_estimate_).
+M17B_FN_COLD F2 clock_update_index(uint32_t* sb, int ssi, uint32_t ck_count)
+{
+    Kalman k = kf_load(sb, F_CK_X0);
+    kf_update(k, (float) ssi, (float) ck_count, true);
+    kf_store(sb, F_CK_X0, k);
+    F2 r; r.x = k.x0; r.y = k.x1;
+    return r;
+}
+
+M17B_FN size_t ring_off(uint32_t p, uint32_t cmask, uint32_t np, uint32_t s)
+{
+    return ((size_t) ((p >> 3) & cmask) * np + s) * 8 + (p & 7);
+}
+
+// FIR history snapshot when the carrier detect gates the filter off
+// (M17Demodulator.h:675-689: demod_filter is not clocked while !dcd_).  snap[j] =
+// the j-th most recent input the filter has seen; k = samples clocked since the
+// last resume (>= 149 unless the carrier dropped again at once).
+M17B_FN_COLD void take_snapshot(float* snap, const float* ring_x, uint32_t np, uint32_t cmask,
+                                uint32_t s, uint32_t pos, int k)
+{
+    if (k < kTapsUsed)
+        for (int j = kTapsUsed - 1; j >= k; --j) snap[(size_t) j * np] = snap[(size_t) (j - k) * np];
+    int n = k < kTapsUsed ? k : kTapsUsed;
+    for (int j = 0; j != n; ++j) snap[(size_t) j * np] = ring_x[ring_off(pos - (uint32_t) j, cmask, np, s)];
+}
+
+// Exact matched filter for the first 149 samples after the filter resumes: taps
+// reach back across the gap into the snapshot (FirFilter.h:28-43 on stale history).
+M17B_FN_COLD float slow_fir(const float* snap, const float* ring_x, uint32_t np, uint32_t cmask,
+                            uint32_t s, uint32_t pos, int k)
+{
+    float result = 0.0f;
+    for (int i = 0; i != kTapsUsed; ++i) {
+        float v = i <= k ? ring_x[ring_off(pos - (uint32_t) i, cmask, np, s)] : snap[(size_t) (i - k - 1) * np];
+        result = add_rn(result, mul_rn(v, M17B_TAB.taps[i]));
+    }
+    return result;
+}
+
+// Util.h:128-145 (llr<float,4>) -> packed (second << 8 | first) int8 pair.  The reference
+// binary-searches 43 thresholds spaced ~1/7 apart; the same lower_bound index is found here
+// from an arithmetic first guess corrected against the thresholds themselves (a copy of the
+// table in shared memory: lanes look up different entries).
+struct LlrTable { float thr[44]; uint32_t val[44]; };
+
+M17B_FN uint32_t llr4(const LlrTable& tab, float sample)
+{
+    float t = (-3.0f < sample) ? sample : -3.0f;      // std::max(MIN_VALUE, sample)
+    float v = (t < 3.0f) ? t : 3.0f;                  // std::min(MAX_VALUE, t)
+    int g = (int) ((v + 3.0f) * 7.0f);                // about the number of thresholds below v
+    g = g < 0 ? 0 : (g > 43 ? 43 : g);
+    while (g > 0 && !(tab.thr[g - 1] < v)) --g;       // lower_bound: first index with !(thr < v)
+    while (g < 43 && tab.thr[g] < v) ++g;
+    if (g == 43) g = 42;
+    return tab.val[g];
+}
+
+// ---------------------------------------------------------------------------
+// scan
+// ---------------------------------------------------------------------------
+
+// Per-lane working set of the scan.
+struct Scan {
+    float re0, im0, re1, im1, l1, l2, level;   // NSlidingDFT bins, DCD accumulators, DCD level
+    float iir0, iir1, limit;                   // limit biquad history / output
+    float idev, offset, evm;
+    float ck_est, ck_sest;
+    uint32_t ck_count;
+    int count, init;
+    int corr_pos, rp, framer_index, gap_k;     // next logical / physical ring write slot
+    int pp, ph;                                // logical / physical slot of the sample being handled
+    int state, swt, si, ssi, csi;
+    bool dcd, dcd_trig, need_reset, need_update, dev_reset, eot, pending;
+    int sync_count, missing;
+    uint32_t vcost;
+    uint32_t sw;                               // packed SyncWord state, 8 bits per word
+};
+
+struct LaneIo {
+    const LlrTable* llr_tab;
+    uint32_t* sb;          // &st[block][0][lane]
+    float* ring;           // [96] column, stride RS (shared memory on the device)
+    float* lim;            // [8] column, stride RS: limit after each sample of the current block
+    float* sw_samples;     // + s, stride np
+    int16_t* llr;          // + s, stride np
+    float* snap;           // + s, stride np
+    const float* ring_y;
+    const float* ring_x;
+    uint32_t np, cmask, s;
+};
+
+#define M17B_UPDATE_VALUES(index_)                                                  \
+    do {                                                                            \
+        F2 od_ = update_values(e.sb, e.ring, z.si, z.pp, z.ph, z.dev_reset);        \
+        z.offset = od_.x; z.idev = od_.y; z.dev_reset = false;                      \
+        z.ssi = (index_);                                                           \
+    } while (0)
+
+M17B_FN int do_sync_step(Scan& z, const LaneIo& e, int k, uint32_t word, float m1, float m2, int* timing)
+{
+    uint32_t f = (z.sw >> (8 * k)) & 0xFF;
+    uint32_t r = sync_step(e.sw_samples + (size_t) (10 * k) * e.np, e.np, e.ring, z.ph, z.pp % 10, z.limit, word, m1, m2, f);
+    z.sw = (z.sw & ~(0xFFu << (8 * k))) | ((r & 0xFF) << (8 * k));
+    *timing = (int) (r & 0xF);
+    uint32_t u = (r >> 8) & 3;
+    return u == 0 ? 0 : (u == 1 ? 1 : -1);
+}
+
+// DataCarrierDetect.h:63-69 (ltrigger 0.1, htrigger 4.0)
+M17B_FN void dcd_update(Scan& z)
+{
+    z.level = (float) ((double) z.level * 0.8 + 0.2 * (double) (z.l1 / z.l2));
+    z.l1 = 0.f; z.l2 = 0.f;
+    z.dcd_trig = z.dcd_trig ? z.level > 0.1f : z.level > 4.0f;
+}
+
+// M17Demodulator.h:274-286 (update_dcd, dcd_on :243-257, dcd_off :259-265)
+M17B_FN void update_dcd(Scan& z, const LaneIo& e)
+{
+    if (!z.dcd && z.dcd_trig) {
+        z.dcd = true;
+        if (z.state == ST_UNLOCKED) {
+            z.sync_count = 0;
+            z.missing = 0;
+            z.framer_index = 0;                                         // framer.reset()
+            e.sb[F_DEC * 32] = (e.sb[F_DEC * 32] & ~0xFFu) | DEC_LSF;    // decoder.reset()
+            z.evm = 0.f;                                                // evm.reset()
+        }
+        z.need_reset = true;
+        z.gap_k = 0;                                                    // filter resumes on stale history
+    } else if (z.dcd && !z.dcd_trig) {
+        z.state = ST_UNLOCKED;
+        z.dcd = false;
+    }
+}
+
+// M17Demodulator.h:288-342
+M17B_FN void do_unlocked(Scan& z, const LaneIo& e)
+{
+    int timing;
+    if (z.missing < 1920) {
+        z.missing += 1;
+        int upd = do_sync_step(z, e, 0, kWordPreamble, 29.f, kLowest, &timing);
+        if (upd) {
+            z.sync_count = 0;
+            z.missing = 0;
+            z.need_reset = true;
+            z.dev_reset = true;
+            z.si = timing;
+            M17B_UPDATE_VALUES(timing);
+            z.state = ST_LSF_SYNC;
+        }
+        return;
+    }
+    int upd = do_sync_step(z, e, 1, kWordLsf, 31.f, -31.f, &timing);
+    if (upd) {
+        z.sync_count = 86;
+        z.missing = 0;
+        z.need_reset = true;
+        z.dev_reset = true;
+        z.si = timing;
+        M17B_UPDATE_VALUES(timing);
+        z.state = ST_FRAME;
+        z.swt = upd < 0 ? SW_STREAM : SW_LSF;
+    }
+    upd = do_sync_step(z, e, 2, kWordPacket, 31.f, -31.f, &timing);
+    if (upd < 0) {
+        z.sync_count = 86;
+        z.missing = 0;
+        z.need_reset = true;
+        z.dev_reset = true;
+        z.si = timing;
+        M17B_UPDATE_VALUES(timing);
+        z.state = ST_FRAME;
+        z.swt = SW_BERT;
+    }
+}
+
+// M17Demodulator.h:349-411 (only called on samples with index() == sample_index)
+M17B_FN void do_lsf_sync(Scan& z, const LaneIo& e)
+{
+    float trig = sync_triggered(e.ring, z.ph, z.limit, kWordPreamble, 29.f, kLowest);
+    if ((double) trig > 0.1) {
+        z.need_update = true;
+        z.sync_count += 1;
+        return;
+    }
+    trig = sync_triggered(e.ring, z.ph, z.limit, kWordLsf, 31.f, -31.f);
+    float bert = sync_triggered(e.ring, z.ph, z.limit, kWordPacket, 31.f, -31.f);
+    if (bert < 0) {
+        z.missing = 0;
+        z.sync_count = 86;
+        z.need_update = true;
+        M17B_UPDATE_VALUES(z.si);
+        z.state = ST_FRAME;
+        z.swt = SW_BERT;
+    } else if ((double) fabsf(trig) > 0.1) {
+        z.missing = 0;
+        z.sync_count = 86;
+        z.need_update = true;
+        M17B_UPDATE_VALUES(z.si);
+        z.state = ST_FRAME;
+        z.swt = trig > 0 ? SW_LSF : SW_STREAM;
+    } else if (++z.missing > 192) {
+        if (z.sync_count >= 10) {
+            z.missing = 0;
+            z.need_update = true;
+        } else {
+            z.sync_count = 0;
+            z.state = ST_UNLOCKED;
+            z.missing = 0;
+            z.dcd_trig = false;              // dcd.unlock()
+        }
+    } else {
+        M17B_UPDATE_VALUES(z.si);
+    }
+}
+
+// M17Demodulator.h:419-482 past the `sync_count < MIN_SYNC_COUNT` gate
+M17B_FN void do_stream_sync(Scan& z, const LaneIo& e)
+{
+    if (sync_triggered(e.ring, z.ph, z.limit, kWordEot, 31.f, kLowest) > 0.1f) {
+        z.swt = SW_STREAM;
+        z.state = ST_FRAME;
+        z.eot = true;
+        z.missing = 0;
+        return;
+    }
+    int timing;
+    int upd = do_sync_step(z, e, 1, kWordLsf, 31.f, -31.f, &timing);
+    if (upd < 0) {
+        z.missing = 0;
+        M17B_UPDATE_VALUES(timing);
+        z.swt = SW_STREAM;
+        z.state = ST_SYNC_WAIT;
+        z.eot = false;
+    } else if (z.sync_count > 86) {
+        if (z.vcost < 80u) {
+            if (!z.missing) z.missing = 1;
+            z.swt = SW_STREAM;
+            z.state = ST_FRAME;
+        } else if (z.eot) {
+            z.state = ST_UNLOCKED;
+            z.dcd_trig = false;
+        } else if (z.missing < 10) {
+            z.missing += 1;
+            z.swt = SW_STREAM;
+            z.state = ST_FRAME;
+        } else {
+            z.state = ST_UNLOCKED;
+            z.dcd_trig = false;
+        }
+        z.eot = false;
+    }
+}
+
+// M17Demodulator.h:488-530 (packet) and :535-574 (BERT) past the MIN_SYNC_COUNT gate
+M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, bool bert)
+{
+    int timing;
+    int upd = do_sync_step(z, e, 2, kWordPacket, 31.f, -31.f, &timing);
+    int swt = bert ? SW_BERT : SW_PACKET;
+    if (bert ? (upd < 0) : (upd != 0)) {
+        z.missing = 0;
+        M17B_UPDATE_VALUES(timing);
+        z.swt = swt;
+        z.state = ST_SYNC_WAIT;
+    } else if (z.sync_count > 86) {
+        if (z.vcost < (bert ? 80u : 60u)) {
+            if (!z.missing) z.missing = 1;
+            z.swt = swt;
+            z.state = ST_FRAME;
+        } else if (z.missing < 10) {
+            z.missing += 1;
+            z.swt = swt;
+            z.state = ST_FRAME;
+        } else {
+            z.state = ST_UNLOCKED;
+            z.dcd_trig = false;
+        }
+    }
+}
+
+// M17Demodulator.h:595-654 up to the decoder call (which decode_kernel performs)
+M17B_FN void do_frame(Scan& z, const LaneIo& e)
+{
+    int idx = z.pp % 10;
+    int diff = z.si - idx;
+    if (diff == 5 || diff == -5) {
+        // ClockRecovery.h:76-88
+        // fmod(v, 10) is v itself for |v| < 10 and v -+ 10 (exact) for |v| < 20; libm otherwise
+        const float v = z.ck_sest + z.ck_est * (float) z.ck_count;
+        const float av = fabsf(v);
+        float csw;
+        if (av < 10.f) csw = v;
+        else if (av < 20.f) csw = v - (v < 0 ? -10.0f : 10.0f);
+        else csw = (float) fmod((double) v, 10.0);      // exact: |result| < 10 has no more bits than v
+        // `if (csw < 0.) csw += 10; else if (csw >= 10) csw -= 10;` in double, then round:
+        // csw + 10 can need more than 24 bits, so keep that one step in double
+        int r;
+        if (csw < 0.f) r = (int) (int8_t) round((double) csw + 10.0);
+        else r = round_half_away(csw);
+        z.csi = wrap_index(r);
+        z.si = z.csi;
+        return;
+    }
+    if (idx != z.si) return;
+
+    float sample = e.ring[z.ph * RS] - z.offset;
+    sample *= z.idev;                                   // polarity is +1 and never changes
+    // SymbolEvm.h:31-51 + StandardDeviation.h:68-72
+    float err;
+    if (sample > 2) err = sample - 3;
+    else if (sample > 0) err = sample - 1;
+    else if (sample > -2) err = sample + 1;
+    else err = sample + 3;
+    const float alpha = (float) (1.0 / 184);
+    z.evm -= z.evm * alpha;
+    z.evm += (err * err) * alpha;
+
+    uint32_t pair = llr4(*e.llr_tab, sample);
+    e.llr[(size_t) (z.framer_index >> 1) * e.np] = (int16_t) pair;      // M17Framer.h:42-53
+    z.framer_index += 2;
+    if (z.framer_index != 368) return;
+    z.framer_index = 0;
+    z.sync_count = 0;
+    z.pending = true;                                   // decoder(...) runs in decode_kernel
+    z.state = ST_TBD;
+}
+
+// Number of upcoming samples on which the state machine provably does nothing but
+// count: `i10` = index() of the next sample.  advance_quiet() applies the counting.
+M17B_FN int quiet_samples(const Scan& z, int i10)
+{
+    int q;
+    switch (z.state) {
+    case ST_UNLOCKED: return 0;
+    case ST_LSF_SYNC: { int d = z.si - i10; q = d < 0 ? d + 10 : d; break; }       // acts when index() == sample_index
+    case ST_STREAM_SYNC: case ST_PACKET_SYNC: case ST_BERT_SYNC:
+        q = 77 - z.sync_count; q = q < 0 ? 0 : q; break;                           // ++sync_count; acts from 78 on
+    case ST_SYNC_WAIT: q = z.sync_count < 86 ? 86 - z.sync_count : 0; break;       // ++sync_count up to 86, then acts
+    case ST_FRAME: {
+        int d = z.si - i10; d = d < 0 ? d + 10 : d;                                // samples until index() == sample_index
+        int a = d >= 5 ? d - 5 : d + 5;                                            // ... until |sample_index - index()| == 5
+        q = d < a ? d : a;
+        break;
+    }
+    default: return 0;
+    }
+    if (z.need_reset || z.need_update) {                                           // :695-709 acts when index() == 0
+        int r = i10 == 0 ? 0 : 10 - i10;
+        q = r < q ? r : q;
+    }
+    return q;
+}
+
+M17B_FN void advance_quiet(Scan& z, int n)
+{
+    z.ck_count += (uint32_t) n;                        // clock_recovery(filtered_sample), ClockRecovery.h:42-45
+    if (z.state == ST_STREAM_SYNC || z.state == ST_PACKET_SYNC || z.state == ST_BERT_SYNC || z.state == ST_SYNC_WAIT)
+        z.sync_count += n;
+}
+
+// One sample of M17Demodulator.h:695-740 (everything between correlator.sample()
+// and the carrier-detect cadence check).
+M17B_FN void event_step(Scan& z, const LaneIo& e)
+{
+    uint32_t* sb = e.sb;
+    if (z.pp % 10 == 0) {               // :695-709
+        if (z.need_reset) {
+            Kalman k; kf_reset(k, (float) z.ssi);          // ClockRecovery.h:33-39
+            kf_store(sb, F_CK_X0, k);
+            z.ck_count = 0;
+            z.csi = z.ssi;
+            z.ck_est = 0.f;
+            z.need_reset = false;
+            z.si = z.ssi;
+        } else if (z.need_update) {
+            F2 r = clock_update_index(sb, z.ssi, z.ck_count);
+            z.ck_sest = r.x;
+            z.csi = wrap_index(round_half_away(z.ck_sest));
+            z.ck_est = r.y;
+            z.ck_count = 0;
+            z.need_update = false;
+        }
+    }
+    z.ck_count++;                       // clock_recovery(filtered_sample), :712
+
+    switch (z.state) {                  // :714-740
+    case ST_UNLOCKED: do_unlocked(z, e); break;
+    case ST_LSF_SYNC: if (z.pp % 10 == z.si) do_lsf_sync(z, e); break;
+    case ST_STREAM_SYNC:
+        z.sync_count += 1;
+        if (z.sync_count >= 78) do_stream_sync(z, e);
+        break;
+    case ST_PACKET_SYNC:
+        z.sync_count += 1;
+        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, false);
+        break;
+    case ST_BERT_SYNC:
+        z.sync_count += 1;
+        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, true);
+        break;
+    case ST_SYNC_WAIT:                  // :582-593
+        if (z.sync_count < 86) z.sync_count += 1;
+        else { z.need_update = true; z.state = ST_FRAME; }
+        break;
+    default: do_frame(z, e); break;
+    }
+}
+
+struct Chunk { float y[8], x[8], o[8]; };
+
+// Dense pass over samples [jb, je) of the block starting at absolute position `base`.
+M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base,
+                         float c0r, float c0i, float c1r, float c1i)
+{
+#pragma unroll
+    for (int j = 0; j != 8; ++j) {
+        if (j < jb || j >= je) continue;
+        {   // dcd(input): SlidingDFT.h:118-132, DataCarrierDetect.h:53-58
+            float delta = c.x[j] - c.o[j];
+            float a = z.re0 + delta, b = z.im0;
+            z.re0 = a * c0r - b * c0i; z.im0 = a * c0i + b * c0r;
+            a = z.re1 + delta; b = z.im1;
+            z.re1 = a * c1r - b * c1i; z.im1 = a * c1i + b * c1r;
+            z.l1 += z.re0 * z.re0 + z.im0 * z.im0;
+            z.l2 += z.re1 * z.re1 + z.im1 * z.im1;
+        }
+        if (!clocked) continue;         // :675-689: the filter and the correlator are not clocked while !dcd_
+        float filtered = c.y[j];        // the matched filter has run speculatively on every sample
+        if (z.gap_k < kTapsUsed) {      // ... which is wrong for 149 samples after a carrier-detect gap
+            filtered = slow_fir(e.snap, e.ring_x, e.np, e.cmask, e.s, base + (uint32_t) j, z.gap_k);
+            z.gap_k++;
+        }
+        {   // correlator.sample(): Correlator.h:43-49, IirFilter.h:26-42
+            float h2 = z.iir1, h1 = z.iir0;
+            float h0 = fabsf(filtered);
+            h0 -= -1.98148851f * h1;
+            h0 -= 0.98165828f * h2;
+            float r = 0.f;
+            r += 4.24433681e-05f * h0;
+            r += 8.48867363e-05f * h1;
+            r += 4.24433681e-05f * h2;
+            z.limit = r;
+            z.iir0 = h0; z.iir1 = h1;
+            e.ring[z.rp * RS] = filtered;
+            e.lim[j * RS] = r;
+            z.rp = z.rp == kRing - 1 ? 0 : z.rp + 1;
+            z.corr_pos = z.corr_pos == 79 ? 0 : z.corr_pos + 1;
+        }
+    }
+}
+
+// Walk this lane from its position towards `head`.  Returns with the lane at head,
+// stopped on a completed frame (FL_PENDING, decode_kernel's turn) or out of budget.
+M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
+{
+    uint32_t* sb = e.sb;
+    uint32_t pos = sb[F_POS * 32];
+    uint32_t fl = sb[F_FLAGS * 32];
+    if (pos == head || (fl & FL_PENDING)) {
+        if (pos != head) ctr_add(&d.ctr->lagging, 1u);
+        return;
+    }
+    uint32_t dpos = sb[F_DPOS * 32];
+
+    Scan z;
+    z.re0 = u2f(sb[F_RE0 * 32]); z.im0 = u2f(sb[F_IM0 * 32]);
+    z.re1 = u2f(sb[F_RE1 * 32]); z.im1 = u2f(sb[F_IM1 * 32]);
+    z.l1 = u2f(sb[F_L1 * 32]); z.l2 = u2f(sb[F_L2 * 32]);
+    z.level = u2f(sb[F_LEVEL * 32]);
+    z.iir0 = u2f(sb[F_IIR0 * 32]); z.iir1 = u2f(sb[F_IIR1 * 32]);
+    z.limit = u2f(sb[F_LIMIT * 32]);
+    z.idev = u2f(sb[F_IDEV * 32]); z.offset = u2f(sb[F_OFFSET * 32]);
+    z.evm = u2f(sb[F_EVM * 32]);
+    z.ck_est = u2f(sb[F_CK_EST * 32]); z.ck_sest = u2f(sb[F_CK_SEST * 32]);
+    z.ck_count = sb[F_CK_COUNT * 32];
+    { uint32_t v = sb[F_CNT * 32]; z.count = v & 0xFFFF; z.init = v >> 16; }
+    { uint32_t v = sb[F_IDX * 32]; z.corr_pos = v & 0xFF; z.framer_index = (v >> 8) & 0xFFFF; z.gap_k = v >> 24; }
+    z.rp = (int) sb[F_RP * 32];
+    z.pp = 0; z.ph = 0;
+    z.state = (fl >> FL_STATE_SHIFT) & 7; z.swt = (fl >> FL_SWT_SHIFT) & 3;
+    z.si = (fl >> FL_SI_SHIFT) & 15; z.ssi = (fl >> FL_SSI_SHIFT) & 15; z.csi = (fl >> FL_CSI_SHIFT) & 15;
+    z.dcd = fl & FL_DCD; z.dcd_trig = fl & FL_DCD_TRIG; z.need_reset = fl & FL_NEED_RESET;
+    z.need_update = fl & FL_NEED_UPDATE; z.dev_reset = fl & FL_DEV_RESET; z.eot = fl & FL_EOT;
+    z.pending = false;
+    z.sync_count = (int) sb[F_SYNC_COUNT * 32]; z.missing = (int) sb[F_MISSING * 32];
+    z.vcost = sb[F_VCOST * 32];
+    z.sw = sb[F_SW * 32];
+
+    for (int k = 0; k != kRing; ++k) e.ring[k * RS] = d.corr_ring[(size_t) k * d.np + e.s];
+    if (dpos != pos)                                        // limits of the samples the dense pass ran ahead by
+        for (int j = (int) (pos & 7); j != 8; ++j) e.lim[j * RS] = d.lim_save[(size_t) j * d.np + e.s];
+
+    const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
+    int budget = kRoundCap;
+
+    while (pos != head && !z.pending && budget > 0) {
+        const uint32_t base = pos & ~7u;
+        const int jb_e = (int) (pos - base);
+        const int jb_d = (int) (dpos - base);               // jb_e <= jb_d <= 8
+        const uint32_t left = head - base;
+        const int je = left < 8u ? (int) left : 8;
+        const bool initializing = z.init != 0;              // :667-673
+        const bool clocked = initializing || z.dcd;
+
+        if (jb_d < je) {
+            Chunk c;
+            const uint32_t cc = base >> 3;
+            const float4* py = reinterpret_cast<const float4*>(e.ring_y + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
+            const float4* px = reinterpret_cast<const float4*>(e.ring_x + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
+            const float4* po = reinterpret_cast<const float4*>(e.ring_x + ((size_t) ((cc - 15) & e.cmask) * e.np + e.s) * 8);
+            float4 a0 = py[0], a1 = py[1], b0 = px[0], b1 = px[1], o0 = po[0], o1 = po[1];
+            c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
+            c.x[0] = b0.x; c.x[1] = b0.y; c.x[2] = b0.z; c.x[3] = b0.w; c.x[4] = b1.x; c.x[5] = b1.y; c.x[6] = b1.z; c.x[7] = b1.w;
+            c.o[0] = o0.x; c.o[1] = o0.y; c.o[2] = o0.z; c.o[3] = o0.w; c.o[4] = o1.x; c.o[5] = o1.y; c.o[6] = o1.z; c.o[7] = o1.w;
+            dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
+            const int n = je - jb_d;
+            if (initializing) z.init -= n;                  // count_ stays 0 while initializing
+            else z.count += n;
+            dpos = base + (uint32_t) je;
+        }
+
+        int j = je;
+        if (z.dcd && !initializing) {
+            // event pass over [jb_e, je): the sample at block offset j sits (dpos - base - j) slots
+            // behind the next write position
+            j = jb_e;
+            int back = (int) (dpos - base) - j;             // >= 1
+            z.pp = z.corr_pos - back; if (z.pp < 0) z.pp += 80;
+            z.ph = z.rp - back; if (z.ph < 0) z.ph += kRing;
+            while (j < je) {
+                int q = quiet_samples(z, z.pp % 10);
+                if (q >= je - j) { advance_quiet(z, je - j); j = je; break; }
+                if (q) {
+                    advance_quiet(z, q);
+                    j += q;
+                    z.pp += q; if (z.pp >= 80) z.pp -= 80;
+                    z.ph += q; if (z.ph >= kRing) z.ph -= kRing;
+                }
+                z.limit = e.lim[j * RS];
+                event_step(z, e);
+                ++j;
+                z.pp = z.pp == 79 ? 0 : z.pp + 1;
+                z.ph = z.ph == kRing - 1 ? 0 : z.ph + 1;
+                if (z.pending) break;
+            }
+        }
+        budget -= j - jb_e;
+        pos = base + (uint32_t) j;
+
+        if (j == 8) {                                       // block complete: cadence checks
+            if (initializing) {
+                if (z.init == 0) {                          // from the next sample on the filter is gated by !dcd_
+                    z.gap_k = kTapsUsed;
+                    take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, kTapsUsed);
+                }
+            } else if (!z.dcd) {
+                if (z.count == 384) {                       // :675-689
+                    update_dcd(z, e);
+                    dcd_update(z);
+                    z.count = 0;
+                }
+            } else if (z.count == 960) {                    // :742-752
+                update_dcd(z, e);
+                z.count = 0;
+                dcd_update(z);
+                if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, z.gap_k);
+            }
+        }
+    }
+    // write back
+    sb[F_POS * 32] = pos;
+    sb[F_DPOS * 32] = dpos;
+    sb[F_RE0 * 32] = f2u(z.re0); sb[F_IM0 * 32] = f2u(z.im0);
+    sb[F_RE1 * 32] = f2u(z.re1); sb[F_IM1 * 32] = f2u(z.im1);
+    sb[F_L1 * 32] = f2u(z.l1); sb[F_L2 * 32] = f2u(z.l2);
+    sb[F_LEVEL * 32] = f2u(z.level);
+    sb[F_IIR0 * 32] = f2u(z.iir0); sb[F_IIR1 * 32] = f2u(z.iir1);
+    sb[F_LIMIT * 32] = f2u(z.limit);
+    sb[F_IDEV * 32] = f2u(z.idev); sb[F_OFFSET * 32] = f2u(z.offset);
+    sb[F_EVM * 32] = f2u(z.evm);
+    sb[F_CK_EST * 32] = f2u(z.ck_est); sb[F_CK_SEST * 32] = f2u(z.ck_sest);
+    sb[F_CK_COUNT * 32] = z.ck_count;
+    sb[F_CNT * 32] = (uint32_t) z.count | ((uint32_t) z.init << 16);
+    sb[F_IDX * 32] = (uint32_t) z.corr_pos | ((uint32_t) z.framer_index << 8) | ((uint32_t) z.gap_k << 24);
+    sb[F_RP * 32] = (uint32_t) z.rp;
+    fl = ((uint32_t) z.state << FL_STATE_SHIFT) | ((uint32_t) z.swt << FL_SWT_SHIFT) | ((uint32_t) z.si << FL_SI_SHIFT) |
+         ((uint32_t) z.ssi << FL_SSI_SHIFT) | ((uint32_t) z.csi << FL_CSI_SHIFT) |
+         (z.dcd ? FL_DCD : 0) | (z.dcd_trig ? FL_DCD_TRIG : 0) | (z.need_reset ? FL_NEED_RESET : 0) |
+         (z.need_update ? FL_NEED_UPDATE : 0) | (z.dev_reset ? FL_DEV_RESET : 0) | (z.eot ? FL_EOT : 0) |
+         (z.pending ? FL_PENDING : 0);
+    sb[F_FLAGS * 32] = fl;
+    sb[F_SYNC_COUNT * 32] = (uint32_t) z.sync_count; sb[F_MISSING * 32] = (uint32_t) z.missing;
+    sb[F_SW * 32] = z.sw;
+    for (int k = 0; k != kRing; ++k) d.corr_ring[(size_t) k * d.np + e.s] = e.ring[k * RS];
+    if (dpos != pos)
+        for (int j = (int) (pos & 7); j != 8; ++j) d.lim_save[(size_t) j * d.np + e.s] = e.lim[j * RS];
+    if (pos != head) ctr_add(&d.ctr->lagging, 1u);
+}
+
+// Fresh-demodulator state of one lane: the member initialisers of M17Demodulator
+// (M17Demodulator.h:148-178) and of its blocks; every other array starts zeroed.
+M17B_FN void init_lane(uint32_t* sb)
+{
+    for (int f = 0; f != NFIELDS; ++f) sb[f * 32] = 0;
+    Kalman k; kf_reset(k, 0.f);                              // KalmanFilter.h:28-31
+    kf_store(sb, F_CK_X0, k); kf_store(sb, F_DMIN_X0, k); kf_store(sb, F_DMAX_X0, k);
+    sb[F_EVM * 32] = f2u(1.0f);                              // RunningStandardDeviation::S{1.0}
+    sb[F_CNT * 32] = 1920u << 16;                            // `initializing`, M17Demodulator.h:659 (per stream)
+    sb[F_IDX * 32] = (uint32_t) kTapsUsed << 24;             // no filter gap pending
+    sb[F_FLAGS * 32] = FL_DEV_RESET | ((uint32_t) ST_UNLOCKED << FL_STATE_SHIFT) | ((uint32_t) SW_LSF << FL_SWT_SHIFT);
+    sb[F_DEC * 32] = DEC_LSF;
+}
+
+// ---------------------------------------------------------------------------
+// frame decode
+// ---------------------------------------------------------------------------
+
+constexpr int kDecThreads = 128;
+#ifdef __CUDACC__
+constexpr int HS = kDecThreads;         // survivor-history column stride
+#else
+constexpr int HS = 1;
+#endif
+
+// CRC16.h:41-62 over the 30 LSF bytes (a column of dec_bytes); 0 means valid.
+M17B_FN_COLD uint32_t crc16_lsf(const uint8_t* lsf, size_t np)
+{
+    uint32_t reg = M17B_TAB.crc_init;
+    for (int n = 0; n != 30; ++n) {
+        uint32_t byte = lsf[(size_t) n * np];
+        for (int i = 0; i != 8; ++i) {
+            uint32_t msb = reg & 0x8000;
+            reg = ((reg << 1) & 0xFFFF) | ((byte >> (7 - i)) & 1);
+            if (msb) reg ^= 0x5935;
+        }
+    }
+    for (int i = 0; i != 16; ++i) {
+        uint32_t msb = reg & 0x8000;
+        reg = (reg << 1) & 0xFFFF;
+        if (msb) reg ^= 0x5935;
+    }
+    return reg;
+}
+
+// One depunctured soft bit through the folded derandomise/deinterleave map.
+M17B_FN int soft_bit(const int16_t* llr, size_t np, int m, int stale)
+{
+    if (m == 0) return 0;
+    if (m == kMapStale) return stale;
+    int k = (m < 0 ? -m : m) - 1;
+    int pair = llr[(size_t) (k >> 1) * np];
+    int v = (k & 1) ? (int) (int8_t) (pair >> 8) : (int) (int8_t) (pair & 0xFF);
+    return m < 0 ? -v : v;
+}
+
+// butterfly J: cost_[J][0] = +7 iff bit 2 of J, cost_[J][1] = +7 iff bit0 ^ bit1 of J
+// (Viterbi.h:72-88 with polynomials 031, 027 and memory J << 1).
+template <int J>
+M17B_FN void butterfly(const int (&m)[16], int (&n)[16], uint32_t& hist, int a0, int a1, int b0, int b1)
+{
+    constexpr bool c0p = (J >> 2) & 1;
+    constexpr bool c1p = ((J ^ (J >> 1)) & 1);
+    const int cost0 = (c0p ? a0 : a1) + (c1p ? b0 : b1);     // sum |cost_ - s|
+    const int cost1 = (c0p ? a1 : a0) + (c1p ? b1 : b0);     // sum |cost_ + s|
+    const int p0 = m[J], p1 = m[J + 8];
+    const int m0 = p0 + cost0, m1 = p0 + cost1, m2 = p1 + cost1, m3 = p1 + cost0;
+    const bool d0 = m0 > m2, d1 = m1 > m3;                   // Viterbi.h:148-149
+    hist |= (uint32_t) d0 << (2 * J);
+    hist |= (uint32_t) d1 << (2 * J + 1);
+    n[2 * J] = d0 ? m2 : m0;
+    n[2 * J + 1] = d1 ? m3 : m1;
+}
+
+// Viterbi.h:181-236.  Writes out_bits(kind) bits MSB-first into out[] (to_byte_array,
+// Util.h:300-318) and returns round(min_metric / 7.f).
+M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale,
+                              uint16_t* hist_col /* stride HS */, uint8_t* out)
+{
+    const int16_t* map = M17B_TAB.vmap[kind];
+    const int n_in = map_len(kind), n_out = out_bits(kind), steps = n_in / 2;
+    int m[16], n[16];
+#pragma unroll
+    for (int i = 0; i != 16; ++i) m[i] = 0x7fffffff / 2;
+    m[0] = 0;
+    for (int t = 0; t != steps; ++t) {
+        int s0 = soft_bit(llr, np, map[2 * t], stale);
+        int s1 = soft_bit(llr, np, map[2 * t + 1], stale);
+        int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+        if (s0) { a0 = abs(7 - s0); a1 = abs(-7 - s0); }
+        if (s1) { b0 = abs(7 - s1); b1 = abs(-7 - s1); }
+        uint32_t h = 0;
+        butterfly<0>(m, n, h, a0, a1, b0, b1); butterfly<1>(m, n, h, a0, a1, b0, b1);
+        butterfly<2>(m, n, h, a0, a1, b0, b1); butterfly<3>(m, n, h, a0, a1, b0, b1);
+        butterfly<4>(m, n, h, a0, a1, b0, b1); butterfly<5>(m, n, h, a0, a1, b0, b1);
+        butterfly<6>(m, n, h, a0, a1, b0, b1); butterfly<7>(m, n, h, a0, a1, b0, b1);
+        hist_col[t * HS] = (uint16_t) h;
+#pragma unroll
+        for (int i = 0; i != 16; ++i) m[i] = n[i];
+    }
+    int min_element = 0, min_cost = m[0];
+#pragma unroll
+    for (int i = 0; i != 16; ++i)
+        if (m[i] < min_cost) { min_cost = m[i]; min_element = i; }
+    uint32_t cost = (uint32_t) (long long) roundf((float) min_cost / 7.0f);
+
+    const int n_bytes = (n_out + 7) / 8;
+    for (int i = 0; i != n_bytes; ++i) out[i] = 0;
+    int next = min_element, index = steps, o = n_out;
+    for (int t = steps; t-- != 0 && o != 0;) {
+        int v = (hist_col[t * HS] >> next) & 1;      // prevState_[next][v] = (next >> 1) | (v << 3)
+        if (index-- <= n_out) { --o; out[o >> 3] |= (uint8_t) ((next & 1) << (7 - (o & 7))); }
+        next = (next >> 1) | (v << 3);
+    }
+    return cost;
+}
+
+M17B_FN_COLD void emit_record(const DevPtrs& d, uint32_t s, uint32_t* sb, unsigned long long sample_pos,
+                              int type, int cost)
+{
+    uint32_t seq = sb[F_SEQ * 32];
+    sb[F_SEQ * 32] = seq + 1;
+    ctr_add(&d.ctr->frames[type], 1ull);
+    uint32_t slot = ctr_add(&d.ctr->rec_count, 1u);
+    if (slot >= d.rec_cap) { ctr_add(&d.ctr->dropped, 1ull); return; }
+    m17b_frame* r = d.recs + slot;
+    r->stream = s; r->seq = seq; r->sample_pos = sample_pos; r->viterbi_cost = cost;
+    r->type = (uint8_t) type; r->pad[0] = r->pad[1] = r->pad[2] = 0;
+    const uint8_t* b = d.dec_bytes + s;
+    for (int i = 0; i != 26; ++i) r->payload[i] = b[(size_t) i * d.np];
+    for (int i = 0; i != 30; ++i) r->lsf[i] = b[(size_t) (26 + i) * d.np];
+}
+
+// unpack_lich, M17FrameDecoder.h:181-215, with Golay24::decode (Golay24.h:203-222).
+// Returns false when a codeword is uncorrectable; lich[] holds whatever was
+// assembled so far either way, like the reference's output_buffer.lich.
+M17B_FN_COLD bool unpack_lich(const int16_t* llr, size_t np, uint8_t* lich)
+{
+    for (int i = 0; i != 6; ++i) lich[i] = 0;
+    int index = 0;
+    for (int i = 0; i != 4; ++i) {
+        uint32_t codeword = 0;
+        for (int j = 0; j != 24; ++j) {
+            int v = soft_bit(llr, np, M17B_TAB.lichmap[i * 24 + j], 0);
+            codeword <<= 1;
+            codeword |= (uint32_t) (v > 0);
+        }
+        uint32_t synd = (codeword >> 1) & 0xffffffu;          // syndrome(input >> 1), Golay24.h:102-112
+        for (int b = 0; b != 12; ++b) { if (synd & 1) synd ^= 0xC75; synd >>= 1; }
+        uint32_t decoded = codeword ^ (M17B_GOLAY[synd] << 1);
+        if (!(popc(synd) < 3 || !(popc(decoded) & 1))) return false;
+        decoded >>= 12;
+        if (i & 1) {
+            lich[index++] |= (uint8_t) (decoded >> 8);
+            lich[index++] = (uint8_t) (decoded & 0xFF);
+        } else {
+            lich[index++] |= (uint8_t) (decoded >> 4);
+            lich[index] = (uint8_t) ((decoded & 0x0F) << 4);
+        }
+    }
+    return true;
+}
+
+// M17FrameDecoder::operator() for one lane whose framer has completed a frame.
+M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t head, unsigned long long head64)
+{
+    uint32_t* sb = d.st + st_index(s, 0);
+    uint32_t fl = sb[F_FLAGS * 32];
+    if (!(fl & FL_PENDING)) return;
+
+    const size_t np = d.np;
+    const int16_t* llr = d.llr + s;
+    uint8_t* bytes = d.dec_bytes + s;                      // rows 0..25 union payload, 26..55 lsf
+    const uint32_t dec = sb[F_DEC * 32];
+    int dec_state = dec & 0xFF;
+    uint32_t lich_segments = (dec >> 8) & 0xFF;
+    int stale = (int) (int8_t) ((dec >> 16) & 0xFF);       // depuncture_buffer element 401
+    uint32_t vcost = sb[F_VCOST * 32];
+    const int swt = (fl >> FL_SWT_SHIFT) & 3;
+    // the frame completed on the last sample the scan consumed: position pos - 1
+    const unsigned long long sample_pos = head64 - (unsigned long long) (head - sb[F_POS * 32]) - 1ull;
+
+    uint8_t out[30];
+
+    // M17FrameDecoder.h:353-392
+    if (swt == SW_LSF) {
+        dec_state = DEC_LSF;
+        // decode_lsf, :154-178
+        vcost = viterbi(0, llr, np, stale, hcol, out);
+        stale = soft_bit(llr, np, M17B_TAB.vmap[0][401], 0);              // depuncture_buffer.lsf[401]
+        for (int i = 0; i != 30; ++i) bytes[(size_t) (26 + i) * np] = out[i];
+        if (crc16_lsf(bytes + 26 * np, np) == 0) {
+            // update_state, :113-136 (bit 111 = byte 13 bit 0, 109 = bit 2, 110 = bit 1)
+            int b111 = out[13] & 1, b109 = (out[13] >> 2) & 1, b110 = (out[13] >> 1) & 1;
+            if (b111) { if (b109) dec_state = DEC_STREAM; }
+            else dec_state = ((b109 << 1) | b110) == 1 ? DEC_BASIC_PACKET : DEC_FULL_PACKET;
+            emit_record(d, s, sb, sample_pos, M17B_FRAME_LSF, (int) vcost);
+        } else {
+            ctr_add(&d.ctr->lsf_crc_fail, 1ull);
+            lich_segments = 0;
+            for (int i = 0; i != 30; ++i) bytes[(size_t) (26 + i) * np] = 0;
+        }
+    } else if (swt == SW_STREAM) {
+        if (dec_state == DEC_LSF) {
+            // decode_lich, :217-262
+            uint8_t lich[6];
+            bool ok = unpack_lich(llr, np, lich);
+            for (int i = 0; i != 6; ++i) bytes[(size_t) i * np] = lich[i];
+            if (!ok) {
+                ctr_add(&d.ctr->golay_fail, 1ull);
+            } else {
+                emit_record(d, s, sb, sample_pos, M17B_FRAME_LICH, 0);
+                uint32_t fragment = (lich[5] >> 5) & 7;
+                if (fragment > 5) {
+                    vcost = 0xFFFFFFFFu;
+                } else {
+                    for (int i = 0; i != 5; ++i) bytes[(size_t) (26 + fragment * 5 + i) * np] = lich[i];
+                    lich_segments |= 1u << fragment;
+                    if ((lich_segments & 0x3F) != 0x3F) {
+                        vcost = 0xFFFFFFFFu;
+                    } else if (crc16_lsf(bytes + 26 * np, np) == 0) {
+                        lich_segments = 0;
+                        dec_state = DEC_STREAM;
+                        vcost = 0;
+                        emit_record(d, s, sb, sample_pos, M17B_FRAME_LSF, 0);
+                    } else {
+                        vcost = 128;
+                    }
+                }
+            }
+        } else if (dec_state == DEC_STREAM) {
+            // decode_stream, :276-289
+            vcost = viterbi(1, llr, np, stale, hcol, out);
+            for (int i = 0; i != 18; ++i) bytes[(size_t) i * np] = out[i];
+            emit_record(d, s, sb, sample_pos, M17B_FRAME_STREAM, (int) vcost);
+        } else {
+            dec_state = DEC_LSF;
+        }
+    } else if (swt == SW_PACKET) {
+        if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) {
+            // decode_packet, :299-315
+            vcost = viterbi(2, llr, np, stale, hcol, out);
+            stale = soft_bit(llr, np, M17B_TAB.vmap[2][401], 0);          // depuncture_buffer.packet[401]
+            for (int i = 0; i != 26; ++i) bytes[(size_t) i * np] = out[i];
+            emit_record(d, s, sb, sample_pos,
+                        dec_state == DEC_BASIC_PACKET ? M17B_FRAME_BASIC_PACKET : M17B_FRAME_FULL_PACKET, (int) vcost);
+            if (out[25] & 0x80) dec_state = DEC_LSF;
+        } else {
+            dec_state = DEC_LSF;
+        }
+    } else {
+        // decode_bert, :264-274
+        dec_state = DEC_BERT;
+        vcost = viterbi(3, llr, np, stale, hcol, out);
+        for (int i = 0; i != 25; ++i) bytes[(size_t) i * np] = out[i];
+        emit_record(d, s, sb, sample_pos, M17B_FRAME_BERT, (int) vcost);
+    }
+
+    sb[F_DEC * 32] = (uint32_t) dec_state | (lich_segments << 8) | ((uint32_t) (uint8_t) (int8_t) stale << 16);
+    sb[F_VCOST * 32] = vcost;
+    // M17Demodulator.h:627-642, unless dcd_off already forced UNLOCKED on the same sample
+    int state = (fl >> FL_STATE_SHIFT) & 7;
+    if (state == ST_TBD) {
+        switch (dec_state) {
+        case DEC_STREAM: state = ST_STREAM_SYNC; break;
+        case DEC_LSF: state = ST_STREAM_SYNC; break;
+        case DEC_BERT: state = ST_BERT_SYNC; break;
+        default: state = ST_PACKET_SYNC; break;
+        }
+    }
+    fl = (fl & ~(7u << FL_STATE_SHIFT) & ~FL_PENDING) | ((uint32_t) state << FL_STATE_SHIFT);
+    sb[F_FLAGS * 32] = fl;
+}
+
+} // namespace m17b

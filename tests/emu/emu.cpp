@@ -1,0 +1,146 @@
+// emu.cpp -- single-lane HOST build of the scan/decode lane logic.  TEST INFRASTRUCTURE ONLY.
+//
+// m17_cxx_demod_b200/csrc/m17b_lane.cuh is written without warp intrinsics, so the same source
+// compiles here with g++ (-ffp-contract=off, baseline x86-64: the same separately rounded IEEE
+// operations the kernels execute under -fmad=false).  This harness re-creates the device data
+// layout in host memory, fills the sample ring with the matched filter in the reference's
+// operation order, and then runs scan_lane()/decode_lane() for every stream in the same rounds
+// m17b_submit()/m17b_sync() launch on the GPU.  tests/test_lane_emulation.py compares the frame
+// records with the CPU oracle.  It lets the kernels' control flow (block/event passes, resume
+// after a pending frame, ragged submits) be checked without a GPU; it is never shipped, and the
+// product library does not contain it.
+#include "m17b_lane.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+namespace m17b {
+ConstTables h_tab;
+uint32_t h_golay[2048];
+}
+
+using namespace m17b;
+
+namespace {
+
+uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
+
+struct Emu {
+    DevPtrs d{};
+    std::vector<uint32_t> st;
+    std::vector<float> ring_y, ring_x, corr_ring, lim_save, sw_samples, fir_snap;
+    std::vector<int16_t> llr;
+    std::vector<uint8_t> dec_bytes;
+    std::vector<m17b_frame> recs;
+    Counters ctr{};
+    LlrTable tab{};
+    uint32_t head = 0;
+    unsigned long long head64 = 0;
+};
+
+void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
+{
+    static bool tables = false;
+    if (!tables) { build_tables(h_tab, h_golay); tables = true; }
+    for (int i = 0; i != 43; ++i) {
+        m.tab.thr[i] = h_tab.llr_thr[i];
+        m.tab.val[i] = (uint32_t) (uint8_t) h_tab.llr_val[i][0] | ((uint32_t) (uint8_t) h_tab.llr_val[i][1] << 8);
+    }
+    DevPtrs& d = m.d;
+    d.n_streams = n_streams;
+    d.np = (n_streams + 127u) & ~127u;
+    d.ring_chunks = next_pow2((max_chunk + kRoundCap + 160 + 16 + 7) / 8);
+    d.rec_cap = (uint32_t) rec_cap;
+    size_t np = d.np;
+    m.st.assign((np / 32) * NFIELDS * 32, 0);
+    m.ring_y.assign((size_t) d.ring_chunks * np * 8, 0.f);
+    m.ring_x.assign((size_t) d.ring_chunks * np * 8, 0.f);
+    m.corr_ring.assign(kRing * np, 0.f);
+    m.lim_save.assign(8 * np, 0.f);
+    m.sw_samples.assign(30 * np, 0.f);
+    m.fir_snap.assign((size_t) kTapsUsed * np, 0.f);
+    m.llr.assign(184 * np, 0);
+    m.dec_bytes.assign(56 * np, 0);
+    m.recs.resize(rec_cap);
+    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
+    d.lim_save = m.lim_save.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
+    d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
+    for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
+}
+
+void round(Emu& m)
+{
+    DevPtrs& d = m.d;
+    m.ctr.lagging = 0;
+    float ring[kRing], lim[8];
+    for (uint32_t s = 0; s != d.n_streams; ++s) {
+        LaneIo e;
+        e.llr_tab = &m.tab;
+        e.sb = d.st + st_index(s, 0);
+        e.ring = ring; e.lim = lim;
+        e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
+        e.ring_y = d.ring_y; e.ring_x = d.ring_x;
+        e.np = d.np; e.cmask = d.ring_chunks - 1; e.s = s;
+        scan_lane(d, e, m.head);
+    }
+    uint16_t hist[244];
+    for (uint32_t s = 0; s != d.n_streams; ++s) decode_lane(d, s, hist, m.head, m.head64);
+}
+
+} // namespace
+
+extern "C" {
+
+// Demodulate [n_streams][n] int16 (row stride `stride`) fed in submits of the given sizes (cycled).
+// Returns the number of records written to out (stream-major order is NOT guaranteed; seq is).
+long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t stride, const uint32_t* chunk_sizes,
+                  size_t n_chunk_sizes, int invert, m17b_frame* out, size_t cap)
+{
+    uint32_t max_chunk = 0;
+    for (size_t i = 0; i != n_chunk_sizes; ++i) max_chunk = std::max(max_chunk, chunk_sizes[i]);
+    Emu m;
+    init(m, (uint32_t) n_streams, max_chunk, cap);
+    // matched filter over the whole capture in the reference's order (FirFilter.h:28-43)
+    std::vector<float> x(n_streams * n), y(n_streams * n);
+    for (size_t s = 0; s != n_streams; ++s) {
+        float* xs = x.data() + s * n; float* ys = y.data() + s * n;
+        for (size_t i = 0; i != n; ++i) {
+            int v = samples[s * stride + i];
+            if (invert) v = (int) (int16_t) (-v);
+            xs[i] = (float) ((double) v / 41067.0);            // apps/m17-demod.cpp:489
+        }
+        for (size_t i = 0; i != n; ++i) {
+            float r = 0.f;
+            size_t kmax = std::min<size_t>(kTapsUsed - 1, i);
+            for (size_t k = 0; k <= kmax; ++k) r = r + xs[i - k] * h_tab.taps[k];
+            for (size_t k = kmax + 1; k < (size_t) kTapsUsed; ++k) r = r + 0.f * h_tab.taps[k];
+            ys[i] = r;
+        }
+    }
+    size_t off = 0, ci = 0;
+    const DevPtrs& d = m.d;
+    while (off < n) {
+        uint32_t c = (uint32_t) std::min<size_t>(chunk_sizes[ci++ % n_chunk_sizes], n - off);
+        for (size_t s = 0; s != n_streams; ++s)
+            for (uint32_t i = 0; i != c; ++i) {
+                size_t o = ring_off(m.head + i, d.ring_chunks - 1, d.np, (uint32_t) s);
+                m.ring_y[o] = y[s * n + off + i];
+                m.ring_x[o] = x[s * n + off + i];
+            }
+        m.head += c; m.head64 += c; off += c;
+        int rounds = (int) (c / kMinFrameSpacing) + 2;
+        for (int r = 0; r != rounds; ++r) round(m);
+        for (int extra = 0; m.ctr.lagging != 0; ++extra) {
+            if (extra == 256) return -1;
+            round(m);
+        }
+    }
+    if (m.ctr.dropped || m.ctr.faults) return -2;
+    size_t k = std::min<size_t>(m.ctr.rec_count, cap);
+    std::memcpy(out, m.recs.data(), k * sizeof(m17b_frame));
+    return (long) k;
+}
+
+}
