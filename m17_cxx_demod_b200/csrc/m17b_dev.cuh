@@ -51,6 +51,8 @@ enum Field : int {
     F_SEQ,
     F_DPOS,         // position of the dense pass (>= F_POS, same 8-sample block)
     F_RP,           // next physical slot of the 96-entry correlator ring
+    F_GAPR,         // position at which the matched filter last resumed after a carrier-detect gap
+    F_GAPDONE,      // outputs after F_GAPR already corrected by fixup_kernel (0..149)
     NFIELDS
 };
 
@@ -66,7 +68,8 @@ constexpr uint32_t FL_NEED_RESET = 1u << 19;
 constexpr uint32_t FL_NEED_UPDATE = 1u << 20;
 constexpr uint32_t FL_DEV_RESET = 1u << 21;
 constexpr uint32_t FL_EOT = 1u << 22;
-constexpr uint32_t FL_PENDING = 1u << 23;
+constexpr uint32_t FL_PENDING = 1u << 23;     // a frame is complete: decode_kernel's turn
+constexpr uint32_t FL_FIXUP = 1u << 24;       // filter outputs after a gap are due: fixup_kernel's turn
 
 enum DemodState : int { ST_UNLOCKED, ST_LSF_SYNC, ST_STREAM_SYNC, ST_PACKET_SYNC, ST_BERT_SYNC, ST_SYNC_WAIT, ST_FRAME, ST_TBD };
 enum DecState : int { DEC_LSF, DEC_STREAM, DEC_BASIC_PACKET, DEC_FULL_PACKET, DEC_BERT };
@@ -80,6 +83,7 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned long long dropped;
     unsigned int rec_count;       // records in the ring
     unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
+    unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
 };
 
 struct DevPtrs {
@@ -88,6 +92,7 @@ struct DevPtrs {
     float* ring_x;
     float* corr_ring;             // [96][Np]
     float* lim_save;              // [8][Np]
+    uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
     float* sw_samples;            // [30][Np]
     float* fir_snap;              // [149][Np]
     int16_t* llr;                 // [184][Np]
@@ -134,6 +139,7 @@ void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_
                  int16_t* tail_out, cudaStream_t s);
 void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
+void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);
 void launch_init_state(const DevPtrs& d, cudaStream_t s);
 cudaError_t configure_kernels();

@@ -261,6 +261,52 @@ decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
     decode_lane(d, s, hist + threadIdx.x, head, head64);
 }
 
+// Matched-filter fix-up after a carrier-detect gap (M17Demodulator.h:675-689: the filter is not
+// clocked while !dcd_, so its first 149 outputs after it resumes see stale history; fir_kernel
+// computed them for contiguous history).  One CTA per waiting stream; thread k recomputes output
+// k in the reference's tap order from the snapshot and the scaled inputs staged in shared memory.
+constexpr int kFixThreads = 160;
+
+__global__ void __launch_bounds__(kFixThreads)
+fixup_kernel(DevPtrs d, uint32_t head)
+{
+    __shared__ float xs[kTapsUsed], snap[kTapsUsed];
+    const uint32_t n_req = d.ctr->fix_count;
+    const uint32_t cmask = d.ring_chunks - 1;
+    const int t = threadIdx.x;
+    for (uint32_t q = blockIdx.x; q < n_req; q += gridDim.x) {
+        const uint32_t s = d.fix_list[q];
+        uint32_t* sb = d.st + st_index(s, 0);
+        const uint32_t R = sb[F_GAPR * 32];
+        const int done = (int) sb[F_GAPDONE * 32];
+        const uint32_t avail = head - R;
+        const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
+        if (t < kTapsUsed) {
+            snap[t] = d.fir_snap[(size_t) t * d.np + s];
+            xs[t] = t < upto ? d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)] : 0.f;
+        }
+        __syncthreads();
+        if (t >= done && t < upto) {
+            float result = 0.0f;
+            for (int i = 0; i != kTapsUsed; ++i) {
+                float v = i <= t ? xs[t - i] : snap[i - t - 1];
+                result = __fadd_rn(result, __fmul_rn(v, c_tab.taps[i]));
+            }
+            d.ring_y[ring_off(R + (uint32_t) t, cmask, d.np, s)] = result;
+        }
+        __syncthreads();
+        if (t == 0) {
+            sb[F_GAPDONE * 32] = (uint32_t) upto;
+            sb[F_FLAGS * 32] &= ~FL_FIXUP;
+        }
+    }
+}
+
+void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
+{
+    fixup_kernel<<<sm_count * 4, kFixThreads, 0, s>>>(d, head);
+}
+
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
 {
     size_t smem = sizeof(uint16_t) * 244 * kDecThreads;

@@ -323,19 +323,6 @@ M17B_FN_COLD void take_snapshot(float* snap, const float* ring_x, uint32_t np, u
     for (int j = 0; j != n; ++j) snap[(size_t) j * np] = ring_x[ring_off(pos - (uint32_t) j, cmask, np, s)];
 }
 
-// Exact matched filter for the first 149 samples after the filter resumes: taps
-// reach back across the gap into the snapshot (FirFilter.h:28-43 on stale history).
-M17B_FN_COLD float slow_fir(const float* snap, const float* ring_x, uint32_t np, uint32_t cmask,
-                            uint32_t s, uint32_t pos, int k)
-{
-    float result = 0.0f;
-    for (int i = 0; i != kTapsUsed; ++i) {
-        float v = i <= k ? ring_x[ring_off(pos - (uint32_t) i, cmask, np, s)] : snap[(size_t) (i - k - 1) * np];
-        result = add_rn(result, mul_rn(v, M17B_TAB.taps[i]));
-    }
-    return result;
-}
-
 // Util.h:128-145 (llr<float,4>) -> packed (second << 8 | first) int8 pair.  The reference
 // binary-searches 43 thresholds spaced ~1/7 apart; the same lower_bound index is found here
 // from an arithmetic first guess corrected against the thresholds themselves (a copy of the
@@ -727,11 +714,10 @@ M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int j
             z.l2 += z.re1 * z.re1 + z.im1 * z.im1;
         }
         if (!clocked) continue;         // :675-689: the filter and the correlator are not clocked while !dcd_
-        float filtered = c.y[j];        // the matched filter has run speculatively on every sample
-        if (z.gap_k < kTapsUsed) {      // ... which is wrong for 149 samples after a carrier-detect gap
-            filtered = slow_fir(e.snap, e.ring_x, e.np, e.cmask, e.s, base + (uint32_t) j, z.gap_k);
-            z.gap_k++;
-        }
+        // the matched filter has run speculatively on every sample; the 149 outputs after a
+        // carrier-detect gap have been replaced by fixup_kernel before the lane gets here
+        float filtered = c.y[j];
+        z.gap_k = z.gap_k < kTapsUsed ? z.gap_k + 1 : z.gap_k;
         {   // correlator.sample(): Correlator.h:43-49, IirFilter.h:26-42
             float h2 = z.iir1, h1 = z.iir0;
             float h0 = fabsf(filtered);
@@ -758,11 +744,14 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
     uint32_t* sb = e.sb;
     uint32_t pos = sb[F_POS * 32];
     uint32_t fl = sb[F_FLAGS * 32];
-    if (pos == head || (fl & FL_PENDING)) {
+    if (pos == head || (fl & (FL_PENDING | FL_FIXUP))) {
         if (pos != head) ctr_add(&d.ctr->lagging, 1u);
         return;
     }
     uint32_t dpos = sb[F_DPOS * 32];
+    uint32_t gap_r = sb[F_GAPR * 32];                       // position the filter last resumed at
+    int gap_done = (int) sb[F_GAPDONE * 32];                // outputs after it already corrected
+    bool fixup = false;
 
     Scan z;
     z.re0 = u2f(sb[F_RE0 * 32]); z.im0 = u2f(sb[F_IM0 * 32]);
@@ -795,7 +784,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
     const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
     int budget = kRoundCap;
 
-    while (pos != head && !z.pending && budget > 0) {
+    while (pos != head && !z.pending && budget > 0) {   // (also left through `break` for a filter fix-up)
         const uint32_t base = pos & ~7u;
         const int jb_e = (int) (pos - base);
         const int jb_d = (int) (dpos - base);               // jb_e <= jb_d <= 8
@@ -804,6 +793,16 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
         const bool initializing = z.init != 0;              // :667-673
         const bool clocked = initializing || z.dcd;
 
+        if (jb_d < je && z.dcd && !initializing && z.gap_k < kTapsUsed) {
+            // outputs gap_k .. of the resumed filter are needed: are they corrected yet?
+            int k_last = (int) (base + (uint32_t) je - 1u - gap_r);
+            if (k_last > kTapsUsed - 1) k_last = kTapsUsed - 1;
+            if (k_last >= gap_done) {
+                fixup = true;                               // fixup_kernel's turn
+                d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
+                break;
+            }
+        }
         if (jb_d < je) {
             Chunk c;
             const uint32_t cc = base >> 3;
@@ -860,6 +859,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
                     update_dcd(z, e);
                     dcd_update(z);
                     z.count = 0;
+                    if (z.dcd) { gap_r = pos; gap_done = 0; }   // the filter resumes with the next sample
                 }
             } else if (z.count == 960) {                    // :742-752
                 update_dcd(z, e);
@@ -889,8 +889,10 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
          ((uint32_t) z.ssi << FL_SSI_SHIFT) | ((uint32_t) z.csi << FL_CSI_SHIFT) |
          (z.dcd ? FL_DCD : 0) | (z.dcd_trig ? FL_DCD_TRIG : 0) | (z.need_reset ? FL_NEED_RESET : 0) |
          (z.need_update ? FL_NEED_UPDATE : 0) | (z.dev_reset ? FL_DEV_RESET : 0) | (z.eot ? FL_EOT : 0) |
-         (z.pending ? FL_PENDING : 0);
+         (z.pending ? FL_PENDING : 0) | (fixup ? FL_FIXUP : 0);
     sb[F_FLAGS * 32] = fl;
+    sb[F_GAPR * 32] = gap_r;
+    sb[F_GAPDONE * 32] = (uint32_t) gap_done;
     sb[F_SYNC_COUNT * 32] = (uint32_t) z.sync_count; sb[F_MISSING * 32] = (uint32_t) z.missing;
     sb[F_SW * 32] = z.sw;
     for (int k = 0; k != kRing; ++k) d.corr_ring[(size_t) k * d.np + e.s] = e.ring[k * RS];
@@ -911,6 +913,35 @@ M17B_FN void init_lane(uint32_t* sb)
     sb[F_IDX * 32] = (uint32_t) kTapsUsed << 24;             // no filter gap pending
     sb[F_FLAGS * 32] = FL_DEV_RESET | ((uint32_t) ST_UNLOCKED << FL_STATE_SHIFT) | ((uint32_t) SW_LSF << FL_SWT_SHIFT);
     sb[F_DEC * 32] = DEC_LSF;
+}
+
+// Filter fix-up for one lane (host emulation: all outputs serially; the device kernel in
+// m17b_kernels.cu spreads the outputs of one request over a CTA).  Corrects ring_y for the
+// outputs [gap_done, min(149, head - R)) after the resume position R.
+M17B_FN void fixup_lane(const DevPtrs& d, uint32_t s, uint32_t head)
+{
+    uint32_t* sb = d.st + st_index(s, 0);
+    const uint32_t R = sb[F_GAPR * 32];
+    const int done = (int) sb[F_GAPDONE * 32];
+    uint32_t avail = head - R;
+    const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
+    const uint32_t cmask = d.ring_chunks - 1;
+    float xs[kTapsUsed];
+    for (int m = 0; m < upto; ++m) xs[m] = d.ring_x[ring_off(R + (uint32_t) m, cmask, d.np, s)];
+    for (int k = done; k < upto; ++k) {
+        float y;
+        {
+            float result = 0.0f;
+            for (int i = 0; i != kTapsUsed; ++i) {
+                float v = i <= k ? xs[k - i] : d.fir_snap[(size_t) (i - k - 1) * d.np + s];
+                result = add_rn(result, mul_rn(v, M17B_TAB.taps[i]));
+            }
+            y = result;
+        }
+        d.ring_y[ring_off(R + (uint32_t) k, cmask, d.np, s)] = y;
+    }
+    sb[F_GAPDONE * 32] = (uint32_t) upto;
+    sb[F_FLAGS * 32] &= ~FL_FIXUP;
 }
 
 // ---------------------------------------------------------------------------
