@@ -228,14 +228,16 @@ scan_kernel(DevPtrs d, uint32_t head)
         tab->val[tid] = (uint32_t) (uint8_t) c_tab.llr_val[tid][0] | ((uint32_t) (uint8_t) c_tab.llr_val[tid][1] << 8);
     }
     __syncthreads();
-    const uint32_t s = blockIdx.x * kScanThreads + tid;
-    if (s >= d.n_streams) return;
+    const uint32_t s = blockIdx.x * kScanThreads + tid;      // < np: padded lanes stay in the warp as helpers
 
     LaneIo e;
     e.llr_tab = tab;
     e.sb = d.st + st_index(s, 0);
     e.ring = ring_s + tid;
     e.lim = lim_s + tid;
+    e.ring_base = ring_s;
+    e.lim_base = lim_s;
+    e.col = tid;
     e.sw_samples = d.sw_samples + s;
     e.llr = d.llr + s;
     e.snap = d.fir_snap + s;
@@ -244,7 +246,7 @@ scan_kernel(DevPtrs d, uint32_t head)
     e.np = d.np;
     e.cmask = d.ring_chunks - 1;
     e.s = s;
-    scan_lane(d, e, head);
+    scan_lane(d, e, head, s < d.n_streams);
 }
 
 void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s)

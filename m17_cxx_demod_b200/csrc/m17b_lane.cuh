@@ -75,6 +75,23 @@ M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { unsigned int o =
 
 constexpr int kRing = 96;               // physical correlator ring (Correlator::buffer_ is 80)
 
+// Warp primitives.  The host build runs one lane at a time: a "warp" of one.
+#ifdef __CUDACC__
+M17B_FN bool warp_any(bool p) { return __any_sync(0xffffffffu, p); }
+M17B_FN uint32_t warp_ballot(bool p) { return __ballot_sync(0xffffffffu, p); }
+M17B_FN int warp_bcast(int v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+M17B_FN void warp_sync() { __syncwarp(); }
+M17B_FN int lane_id() { return (int) (threadIdx.x & 31); }
+M17B_FN int first_set(uint32_t m) { return __ffs((int) m) - 1; }
+#else
+M17B_FN bool warp_any(bool p) { return p; }
+M17B_FN uint32_t warp_ballot(bool p) { return p ? 1u : 0u; }
+M17B_FN int warp_bcast(int v, int) { return v; }
+M17B_FN void warp_sync() {}
+M17B_FN int lane_id() { return 0; }
+M17B_FN int first_set(uint32_t m) { return __builtin_ffs((int) m) - 1; }
+#endif
+
 // ---------------------------------------------------------------------------
 // Kalman filters
 // ---------------------------------------------------------------------------
@@ -367,6 +384,9 @@ struct LaneIo {
     uint32_t* sb;          // &st[block][0][lane]
     float* ring;           // [96] column, stride RS (shared memory on the device)
     float* lim;            // [8] column, stride RS: limit after each sample of the current block
+    float* ring_base;      // column 0 of the CTA's rings / limits and this lane's column number:
+    float* lim_base;       //   lanes read each other's columns when they share a search (corr_bit)
+    int col;
     float* sw_samples;     // + s, stride np
     int16_t* llr;          // + s, stride np
     float* snap;           // + s, stride np
@@ -614,16 +634,54 @@ M17B_FN void do_frame(Scan& z, const LaneIo& e)
     z.state = ST_TBD;
 }
 
-// Number of upcoming samples on which the state machine provably does nothing but
-// count: `i10` = index() of the next sample.  advance_quiet() applies the counting.
-M17B_FN int quiet_samples(const Scan& z, int i10)
+// Sync-word trigger masks of one 8-sample block: bit 8 w + j is set when sync word w
+// (0 preamble, 1 LSF/stream, 2 packet/BERT, 3 EOT) triggers on block sample j
+// (Correlator.h:150-157 returns non-zero).  Computed by corr_masks(); kNoMasks = not computed.
+constexpr uint64_t kNoMasks = ~0ull;
+
+M17B_FN bool sw_trig(const Scan& z, int k) { return (z.sw >> (8 * k + 4)) & 1; }
+
+// block-sample index of the first set bit at or after j, 8 if none
+M17B_FN int next_bit(uint32_t m8, int j)
 {
+    uint32_t m = (m8 & 0xFFu) >> j;
+    return m ? j + first_set(m) : 8;
+}
+
+// Number of upcoming samples on which the state machine provably does nothing but
+// count: `i10` = index() of the next sample, j its offset in the block, `masks` the
+// block's trigger masks.  advance_quiet() applies the counting.
+M17B_FN int quiet_samples(const Scan& z, int i10, int j, uint64_t masks)
+{
+    const bool have = masks != kNoMasks;
+    const uint32_t mk = (uint32_t) masks;
     int q;
     switch (z.state) {
-    case ST_UNLOCKED: return 0;
+    case ST_UNLOCKED:                                                              // :288-342 looks for a sync word on every sample
+        if (!have) return 0;
+        if (z.missing < 1920) {
+            if (sw_trig(z, 0)) return 0;
+            q = next_bit(mk, j) - j;
+            int lim = 1920 - z.missing;                                            // then the search changes words
+            q = q < lim ? q : lim;
+        } else {
+            if (sw_trig(z, 1) || sw_trig(z, 2)) return 0;
+            q = next_bit((mk >> 8) | (mk >> 16), j) - j;
+        }
+        break;
     case ST_LSF_SYNC: { int d = z.si - i10; q = d < 0 ? d + 10 : d; break; }       // acts when index() == sample_index
-    case ST_STREAM_SYNC: case ST_PACKET_SYNC: case ST_BERT_SYNC:
-        q = 77 - z.sync_count; q = q < 0 ? 0 : q; break;                           // ++sync_count; acts from 78 on
+    case ST_STREAM_SYNC: case ST_PACKET_SYNC: case ST_BERT_SYNC: {
+        q = 77 - z.sync_count; q = q < 0 ? 0 : q;                                  // ++sync_count; acts from 78 on
+        const int k = z.state == ST_STREAM_SYNC ? 1 : 2;
+        if (have && !sw_trig(z, k) && j + q < 8) {
+            // inside the window a sample still does nothing unless a word triggers or sync_count passes 86
+            uint32_t m = z.state == ST_STREAM_SYNC ? ((mk >> 8) | (mk >> 24)) : (mk >> 16);
+            int qb = next_bit(m, j + q) - j;
+            int qt = 86 - z.sync_count; qt = qt < 0 ? 0 : qt;
+            q = qb < qt ? qb : qt;
+        }
+        break;
+    }
     case ST_SYNC_WAIT: q = z.sync_count < 86 ? 86 - z.sync_count : 0; break;       // ++sync_count up to 86, then acts
     case ST_FRAME: {
         int d = z.si - i10; d = d < 0 ? d + 10 : d;                                // samples until index() == sample_index
@@ -645,6 +703,21 @@ M17B_FN void advance_quiet(Scan& z, int n)
     z.ck_count += (uint32_t) n;                        // clock_recovery(filtered_sample), ClockRecovery.h:42-45
     if (z.state == ST_STREAM_SYNC || z.state == ST_PACKET_SYNC || z.state == ST_BERT_SYNC || z.state == ST_SYNC_WAIT)
         z.sync_count += n;
+    else if (z.state == ST_UNLOCKED && z.missing < 1920)
+        z.missing += n;                                // :291-293
+}
+
+// Trigger masks for the block of the lane whose ring / limit columns are given: helper t of 32
+// evaluates sync word t >> 3 on block sample t & 7 (ph0 = physical ring slot of block sample 0)
+// with exactly the arithmetic of sync_triggered().
+M17B_FN bool corr_bit(const float* ring, const float* lim, int ph0, int t)
+{
+    const int w = t >> 3, j = t & 7;
+    int ph = ph0 + j; ph = ph >= kRing ? ph - kRing : ph;
+    const uint32_t word = w == 0 ? kWordPreamble : w == 1 ? kWordLsf : w == 2 ? kWordPacket : kWordEot;
+    const float m1 = w == 0 ? 29.f : 31.f;
+    const float m2 = (w == 0 || w == 3) ? kLowest : -31.f;
+    return sync_triggered(ring, ph, lim[j * RS], word, m1, m2) != 0;
 }
 
 // One sample of M17Demodulator.h:695-740 (everything between correlator.sample()
@@ -737,23 +810,30 @@ M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int j
     }
 }
 
-// Walk this lane from its position towards `head`.  Returns with the lane at head,
-// stopped on a completed frame (FL_PENDING, decode_kernel's turn) or out of budget.
-M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
+// Walk this lane from its position towards `head`; on return the lane is at head, stopped on
+// a completed frame (FL_PENDING, decode_kernel's turn), waiting for a filter fix-up (FL_FIXUP)
+// or out of budget.  Called by all 32 lanes of a warp together (`valid` = the lane has a stream):
+// the block loop is warp-synchronous so that the lanes can evaluate the sync-word correlations of
+// a searching lane's block between them (corr_bit).
+M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool valid)
 {
     uint32_t* sb = e.sb;
-    uint32_t pos = sb[F_POS * 32];
-    uint32_t fl = sb[F_FLAGS * 32];
-    if (pos == head || (fl & (FL_PENDING | FL_FIXUP))) {
-        if (pos != head) ctr_add(&d.ctr->lagging, 1u);
-        return;
-    }
-    uint32_t dpos = sb[F_DPOS * 32];
-    uint32_t gap_r = sb[F_GAPR * 32];                       // position the filter last resumed at
-    int gap_done = (int) sb[F_GAPDONE * 32];                // outputs after it already corrected
+    uint32_t pos = valid ? sb[F_POS * 32] : head;
+    uint32_t fl = valid ? sb[F_FLAGS * 32] : 0u;
+    bool active = pos != head && !(fl & (FL_PENDING | FL_FIXUP));
+    if (pos != head && !active) ctr_add(&d.ctr->lagging, 1u);
+    const bool loaded = active;
+    uint32_t dpos = pos;
+    uint32_t gap_r = 0;                                     // position the filter last resumed at
+    int gap_done = 0;                                       // outputs after it already corrected
     bool fixup = false;
 
     Scan z;
+    memset(&z, 0, sizeof(z));
+    if (active) {
+    dpos = sb[F_DPOS * 32];
+    gap_r = sb[F_GAPR * 32];
+    gap_done = (int) sb[F_GAPDONE * 32];
     z.re0 = u2f(sb[F_RE0 * 32]); z.im0 = u2f(sb[F_IM0 * 32]);
     z.re1 = u2f(sb[F_RE1 * 32]); z.im1 = u2f(sb[F_IM1 * 32]);
     z.l1 = u2f(sb[F_L1 * 32]); z.l2 = u2f(sb[F_L2 * 32]);
@@ -767,12 +847,10 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
     { uint32_t v = sb[F_CNT * 32]; z.count = v & 0xFFFF; z.init = v >> 16; }
     { uint32_t v = sb[F_IDX * 32]; z.corr_pos = v & 0xFF; z.framer_index = (v >> 8) & 0xFFFF; z.gap_k = v >> 24; }
     z.rp = (int) sb[F_RP * 32];
-    z.pp = 0; z.ph = 0;
     z.state = (fl >> FL_STATE_SHIFT) & 7; z.swt = (fl >> FL_SWT_SHIFT) & 3;
     z.si = (fl >> FL_SI_SHIFT) & 15; z.ssi = (fl >> FL_SSI_SHIFT) & 15; z.csi = (fl >> FL_CSI_SHIFT) & 15;
     z.dcd = fl & FL_DCD; z.dcd_trig = fl & FL_DCD_TRIG; z.need_reset = fl & FL_NEED_RESET;
     z.need_update = fl & FL_NEED_UPDATE; z.dev_reset = fl & FL_DEV_RESET; z.eot = fl & FL_EOT;
-    z.pending = false;
     z.sync_count = (int) sb[F_SYNC_COUNT * 32]; z.missing = (int) sb[F_MISSING * 32];
     z.vcost = sb[F_VCOST * 32];
     z.sw = sb[F_SW * 32];
@@ -780,95 +858,137 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head)
     for (int k = 0; k != kRing; ++k) e.ring[k * RS] = d.corr_ring[(size_t) k * d.np + e.s];
     if (dpos != pos)                                        // limits of the samples the dense pass ran ahead by
         for (int j = (int) (pos & 7); j != 8; ++j) e.lim[j * RS] = d.lim_save[(size_t) j * d.np + e.s];
+    }
 
     const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
     int budget = kRoundCap;
 
-    while (pos != head && !z.pending && budget > 0) {   // (also left through `break` for a filter fix-up)
-        const uint32_t base = pos & ~7u;
-        const int jb_e = (int) (pos - base);
-        const int jb_d = (int) (dpos - base);               // jb_e <= jb_d <= 8
-        const uint32_t left = head - base;
-        const int je = left < 8u ? (int) left : 8;
-        const bool initializing = z.init != 0;              // :667-673
-        const bool clocked = initializing || z.dcd;
+    while (warp_any(active)) {
+        uint32_t base = 0;
+        int jb_e = 0, je = 0, ph0 = 0;
+        bool initializing = false, go = false, need = false;
 
-        if (jb_d < je && z.dcd && !initializing && z.gap_k < kTapsUsed) {
-            // outputs gap_k .. of the resumed filter are needed: are they corrected yet?
-            int k_last = (int) (base + (uint32_t) je - 1u - gap_r);
-            if (k_last > kTapsUsed - 1) k_last = kTapsUsed - 1;
-            if (k_last >= gap_done) {
-                fixup = true;                               // fixup_kernel's turn
-                d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
-                break;
+        if (active) {
+            base = pos & ~7u;
+            jb_e = (int) (pos - base);
+            const int jb_d = (int) (dpos - base);           // jb_e <= jb_d <= 8
+            const uint32_t left = head - base;
+            je = left < 8u ? (int) left : 8;
+            initializing = z.init != 0;                     // :667-673
+            const bool clocked = initializing || z.dcd;
+            go = true;
+
+            if (jb_d < je && z.dcd && !initializing && z.gap_k < kTapsUsed) {
+                // outputs gap_k .. of the resumed filter are needed: are they corrected yet?
+                int k_last = (int) (base + (uint32_t) je - 1u - gap_r);
+                if (k_last > kTapsUsed - 1) k_last = kTapsUsed - 1;
+                if (k_last >= gap_done) {
+                    fixup = true;                           // fixup_kernel's turn
+                    d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
+                    go = false;
+                    active = false;
+                }
+            }
+            if (go && jb_d < je) {
+                Chunk c;
+                const uint32_t cc = base >> 3;
+                const float4* py = reinterpret_cast<const float4*>(e.ring_y + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
+                const float4* px = reinterpret_cast<const float4*>(e.ring_x + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
+                const float4* po = reinterpret_cast<const float4*>(e.ring_x + ((size_t) ((cc - 15) & e.cmask) * e.np + e.s) * 8);
+                float4 a0 = py[0], a1 = py[1], b0 = px[0], b1 = px[1], o0 = po[0], o1 = po[1];
+                c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
+                c.x[0] = b0.x; c.x[1] = b0.y; c.x[2] = b0.z; c.x[3] = b0.w; c.x[4] = b1.x; c.x[5] = b1.y; c.x[6] = b1.z; c.x[7] = b1.w;
+                c.o[0] = o0.x; c.o[1] = o0.y; c.o[2] = o0.z; c.o[3] = o0.w; c.o[4] = o1.x; c.o[5] = o1.y; c.o[6] = o1.z; c.o[7] = o1.w;
+                dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
+                const int n = je - jb_d;
+                if (initializing) z.init -= n;              // count_ stays 0 while initializing
+                else z.count += n;
+                dpos = base + (uint32_t) je;
+            }
+            if (go && z.dcd && !initializing) {
+                // does the state machine look for sync words on (nearly) every sample of this block?
+                need = z.state == ST_UNLOCKED ||
+                       ((z.state == ST_STREAM_SYNC || z.state == ST_PACKET_SYNC || z.state == ST_BERT_SYNC) &&
+                        z.sync_count + (je - jb_e) >= 78);
+                ph0 = z.rp - (int) (dpos - base); if (ph0 < 0) ph0 += kRing;
             }
         }
-        if (jb_d < je) {
-            Chunk c;
-            const uint32_t cc = base >> 3;
-            const float4* py = reinterpret_cast<const float4*>(e.ring_y + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
-            const float4* px = reinterpret_cast<const float4*>(e.ring_x + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
-            const float4* po = reinterpret_cast<const float4*>(e.ring_x + ((size_t) ((cc - 15) & e.cmask) * e.np + e.s) * 8);
-            float4 a0 = py[0], a1 = py[1], b0 = px[0], b1 = px[1], o0 = po[0], o1 = po[1];
-            c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
-            c.x[0] = b0.x; c.x[1] = b0.y; c.x[2] = b0.z; c.x[3] = b0.w; c.x[4] = b1.x; c.x[5] = b1.y; c.x[6] = b1.z; c.x[7] = b1.w;
-            c.o[0] = o0.x; c.o[1] = o0.y; c.o[2] = o0.z; c.o[3] = o0.w; c.o[4] = o1.x; c.o[5] = o1.y; c.o[6] = o1.z; c.o[7] = o1.w;
-            dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
-            const int n = je - jb_d;
-            if (initializing) z.init -= n;                  // count_ stays 0 while initializing
-            else z.count += n;
-            dpos = base + (uint32_t) je;
-        }
 
-        int j = je;
-        if (z.dcd && !initializing) {
-            // event pass over [jb_e, je): the sample at block offset j sits (dpos - base - j) slots
-            // behind the next write position
-            j = jb_e;
-            int back = (int) (dpos - base) - j;             // >= 1
-            z.pp = z.corr_pos - back; if (z.pp < 0) z.pp += 80;
-            z.ph = z.rp - back; if (z.ph < 0) z.ph += kRing;
-            while (j < je) {
-                int q = quiet_samples(z, z.pp % 10);
-                if (q >= je - j) { advance_quiet(z, je - j); j = je; break; }
-                if (q) {
-                    advance_quiet(z, q);
-                    j += q;
-                    z.pp += q; if (z.pp >= 80) z.pp -= 80;
-                    z.ph += q; if (z.ph >= kRing) z.ph -= kRing;
-                }
-                z.limit = e.lim[j * RS];
-                event_step(z, e);
-                ++j;
-                z.pp = z.pp == 79 ? 0 : z.pp + 1;
-                z.ph = z.ph == kRing - 1 ? 0 : z.ph + 1;
-                if (z.pending) break;
+        // sync-word trigger masks for the lanes that search, one lane's block at a time: 4 words x 8
+        // samples = one correlation per helper lane
+        uint64_t masks = kNoMasks;
+        uint32_t todo = warp_ballot(need);
+        if (todo) {
+            warp_sync();                                    // the searching lanes' ring / limit columns are written
+            while (todo) {
+                const int L = first_set(todo);
+                todo &= todo - 1;
+                const int col = warp_bcast(e.col, L);
+                const int p0 = warp_bcast(ph0, L);
+#ifdef __CUDACC__
+                const uint32_t mk = warp_ballot(corr_bit(e.ring_base + col, e.lim_base + col, p0, lane_id()));
+#else
+                uint32_t mk = 0;
+                for (int t = 0; t != 32; ++t) mk |= (uint32_t) corr_bit(e.ring_base + col, e.lim_base + col, p0, t) << t;
+#endif
+                if (lane_id() == L) masks = mk;
             }
         }
-        budget -= j - jb_e;
-        pos = base + (uint32_t) j;
 
-        if (j == 8) {                                       // block complete: cadence checks
-            if (initializing) {
-                if (z.init == 0) {                          // from the next sample on the filter is gated by !dcd_
-                    z.gap_k = kTapsUsed;
-                    take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, kTapsUsed);
+        if (go) {
+            int j = je;
+            if (z.dcd && !initializing) {
+                // event pass over [jb_e, je): the sample at block offset j sits (dpos - base - j) slots
+                // behind the next write position
+                j = jb_e;
+                int back = (int) (dpos - base) - j;         // >= 1
+                z.pp = z.corr_pos - back; if (z.pp < 0) z.pp += 80;
+                z.ph = z.rp - back; if (z.ph < 0) z.ph += kRing;
+                while (j < je) {
+                    int q = quiet_samples(z, z.pp % 10, j, masks);
+                    if (q >= je - j) { advance_quiet(z, je - j); j = je; break; }
+                    if (q) {
+                        advance_quiet(z, q);
+                        j += q;
+                        z.pp += q; if (z.pp >= 80) z.pp -= 80;
+                        z.ph += q; if (z.ph >= kRing) z.ph -= kRing;
+                    }
+                    z.limit = e.lim[j * RS];
+                    event_step(z, e);
+                    ++j;
+                    z.pp = z.pp == 79 ? 0 : z.pp + 1;
+                    z.ph = z.ph == kRing - 1 ? 0 : z.ph + 1;
+                    if (z.pending) break;
                 }
-            } else if (!z.dcd) {
-                if (z.count == 384) {                       // :675-689
+            }
+            budget -= j - jb_e;
+            pos = base + (uint32_t) j;
+
+            if (j == 8) {                                   // block complete: cadence checks
+                if (initializing) {
+                    if (z.init == 0) {                      // from the next sample on the filter is gated by !dcd_
+                        z.gap_k = kTapsUsed;
+                        take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, kTapsUsed);
+                    }
+                } else if (!z.dcd) {
+                    if (z.count == 384) {                   // :675-689
+                        update_dcd(z, e);
+                        dcd_update(z);
+                        z.count = 0;
+                        if (z.dcd) { gap_r = pos; gap_done = 0; }   // the filter resumes with the next sample
+                    }
+                } else if (z.count == 960) {                // :742-752
                     update_dcd(z, e);
-                    dcd_update(z);
                     z.count = 0;
-                    if (z.dcd) { gap_r = pos; gap_done = 0; }   // the filter resumes with the next sample
+                    dcd_update(z);
+                    if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, z.gap_k);
                 }
-            } else if (z.count == 960) {                    // :742-752
-                update_dcd(z, e);
-                z.count = 0;
-                dcd_update(z);
-                if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, z.gap_k);
             }
+            active = pos != head && !z.pending && budget > 0;
         }
     }
+    if (!loaded) return;
+
     // write back
     sb[F_POS * 32] = pos;
     sb[F_DPOS * 32] = dpos;

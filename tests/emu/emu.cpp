@@ -82,11 +82,11 @@ void round(Emu& m)
         LaneIo e;
         e.llr_tab = &m.tab;
         e.sb = d.st + st_index(s, 0);
-        e.ring = ring; e.lim = lim;
+        e.ring = ring; e.lim = lim; e.ring_base = ring; e.lim_base = lim; e.col = 0;
         e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
         e.ring_y = d.ring_y; e.ring_x = d.ring_x;
         e.np = d.np; e.cmask = d.ring_chunks - 1; e.s = s;
-        scan_lane(d, e, m.head);
+        scan_lane(d, e, m.head, true);
     }
     uint16_t hist[244];
     for (uint32_t s = 0; s != d.n_streams; ++s) decode_lane(d, s, hist, m.head, m.head64);
