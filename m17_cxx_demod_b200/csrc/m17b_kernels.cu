@@ -83,32 +83,36 @@ __device__ __forceinline__ float scale_sample(int v)
 
 constexpr int kFirStreams = 32;     // streams per CTA (one per lane)
 constexpr int kFirWarps = 8;
-constexpr int kFirOut = 16;         // outputs per thread
-constexpr int kFirTile = kFirWarps * kFirOut;      // 128 positions per CTA
+constexpr int kFirOut = 16;         // outputs per thread and pass
+constexpr int kFirPass = kFirWarps * kFirOut;      // 128 positions per pass
+constexpr int kFirPasses = 2;
+constexpr int kFirTile = kFirPass * kFirPasses;    // 256 positions per CTA
 constexpr int kFirHalo = 160;
-constexpr int kFirRow = kFirTile + kFirHalo + 1;   // 289: odd stride -> conflict-free columns
+constexpr int kFirCols = kFirTile + kFirHalo;      // 416 staged samples per stream
+constexpr int kFirRow = kFirCols + 1;              // 417: odd stride -> conflict-free columns
+constexpr int kFirLoop = 9;                        // taps 0..143 in a rolled loop of 16, 144..148 unrolled
 
-template <int I, bool FMA>
-struct FirStep {
-    // Tap I of the filter for 16 consecutive outputs held in acc[]; w[] is a
-    // 16-entry register window: slot (k & 15) holds sample t0 + k, k = r - I.
-    __device__ __forceinline__ static void run(float (&acc)[kFirOut], float (&w)[kFirOut], const float* row)
+// One tap for 16 consecutive outputs held in acc[]; w[] is a 16-entry register window: slot
+// (k & 15) holds sample t0 + k.  Tap index I = 16 * it + K; rowp = row - 16 * it.
+template <int K, int KEND, bool FMA>
+struct FirTaps {
+    __device__ __forceinline__ static void run(float (&acc)[kFirOut], float (&w)[kFirOut], const float* rowp, const float* tp)
     {
-        if constexpr (I > 0) w[(16 - (I & 15)) & 15] = row[-I];
-        constexpr float tap = rrc_tap(I);
+        w[(16 - K) & 15] = rowp[-K];               // sample t0 - I replaces t0 + 16 - I
+        const float tap = tp[K];
 #pragma unroll
         for (int r = 0; r != kFirOut; ++r) {
-            float x = w[(r - I) & 15];
+            float x = w[(r - K) & 15];
             acc[r] = FMA ? __fmaf_rn(x, tap, acc[r]) : __fadd_rn(acc[r], __fmul_rn(x, tap));
         }
-        if constexpr (I + 1 < kTapsUsed) FirStep<I + 1, FMA>::run(acc, w, row);
+        if constexpr (K + 1 < KEND) FirTaps<K + 1, KEND, FMA>::run(acc, w, rowp, tp);
     }
 };
 
 template <bool FMA>
 __global__ void __launch_bounds__(kFirWarps * 32)
 fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_new,
-           const int16_t* __restrict__ tail, uint32_t head, int invert)
+           const int16_t* __restrict__ tail, uint32_t head, int invert, int aligned)
 {
     extern __shared__ float xs[];                  // [32][kFirRow]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -117,39 +121,71 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
     const uint32_t tb = b0 + blockIdx.y * kFirTile;          // first position of this tile
     const int rel0 = (int) (tb - head) - kFirHalo;            // input index of tile column 0
 
-    // stage [tb-160, tb+128) of 32 streams, scaled to float
-    for (int e = tid; e < kFirStreams * (kFirTile + kFirHalo); e += kFirWarps * 32) {
-        int sl = e / (kFirTile + kFirHalo), t = e - sl * (kFirTile + kFirHalo);
-        uint32_t s = s0 + sl;
-        int rel = rel0 + t;
-        int v = 0;
-        if (s < d.n_streams) {
-            if (rel >= 0) { if ((uint32_t) rel < n_new) v = in[(size_t) s * stride + rel]; }
-            else if (rel >= -kTailLen) v = tail[(size_t) s * kTailLen + (kTailLen + rel)];
+    // stage [tb-160, tb+256) of 32 streams, scaled to float: lane = stream, 16 samples (one
+    // 32-byte sector of int16) per thread and step
+    {
+        const uint32_t s = s0 + lane;
+        const bool live = s < d.n_streams;
+        float* dst = xs + lane * kFirRow;
+        const int16_t* src_in = in + (size_t) s * stride;
+        const int16_t* src_tail = tail + (size_t) s * kTailLen + kTailLen;
+        for (int g = warp; g < kFirCols / 16; g += kFirWarps) {
+            const int t = g * 16, rel = rel0 + t;
+            int v[16];
+            if (aligned && live && (rel + 16 <= 0 ? rel >= -kTailLen : (rel >= 0 && (uint32_t) rel + 16u <= n_new))) {
+                const uint4* p = reinterpret_cast<const uint4*>(rel < 0 ? src_tail + rel : src_in + rel);
+                uint4 q0 = p[0], q1 = p[1];
+                const uint32_t u[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                for (int k = 0; k != 8; ++k) { v[2 * k] = (int) (int16_t) (u[k] & 0xFFFF); v[2 * k + 1] = (int) (int16_t) (u[k] >> 16); }
+            } else {
+#pragma unroll
+                for (int k = 0; k != 16; ++k) {
+                    int r = rel + k, x = 0;
+                    if (live) {
+                        if (r >= 0) { if ((uint32_t) r < n_new) x = src_in[r]; }
+                        else if (r >= -kTailLen) x = src_tail[r];
+                    }
+                    v[k] = x;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k != 16; ++k) {
+                int x = v[k];
+                if (invert) x = (int) (int16_t) (-x);                 // int16 `sample *= -1`
+                dst[t + k] = scale_sample(x);
+            }
         }
-        if (invert) v = (int) (int16_t) (-v);                 // int16 `sample *= -1`
-        xs[sl * kFirRow + t] = scale_sample(v);
     }
     __syncthreads();
 
-    const float* row = xs + lane * kFirRow + kFirHalo + warp * kFirOut;     // sample t0
-    float acc[kFirOut], w[kFirOut];
-#pragma unroll
-    for (int r = 0; r != kFirOut; ++r) { acc[r] = 0.0f; w[r] = row[r]; }
-    FirStep<0, FMA>::run(acc, w, row);
-
     const uint32_t s = s0 + lane;
-    const uint32_t c = ((tb >> 3) + warp * (kFirOut / 8)) & (d.ring_chunks - 1);
+    const uint32_t cmask = d.ring_chunks - 1;
+#pragma unroll 1
+    for (int pass = 0; pass != kFirPasses; ++pass) {
+        const int o0 = pass * kFirPass + warp * kFirOut;              // first output of this thread in the tile
+        if (tb + (uint32_t) o0 >= head + n_new) break;                // nothing new from here on (warp-uniform)
+        const float* row = xs + lane * kFirRow + kFirHalo + o0;        // sample t0
+        float acc[kFirOut], w[kFirOut];
 #pragma unroll
-    for (int k = 0; k != kFirOut / 8; ++k) {
-        uint32_t cc = (c + k) & (d.ring_chunks - 1);
-        size_t o = ((size_t) cc * d.np + s) * 8;
-        float4* py = reinterpret_cast<float4*>(d.ring_y + o);
-        float4* px = reinterpret_cast<float4*>(d.ring_x + o);
-        py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
-        py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
-        px[0] = make_float4(row[8 * k + 0], row[8 * k + 1], row[8 * k + 2], row[8 * k + 3]);
-        px[1] = make_float4(row[8 * k + 4], row[8 * k + 5], row[8 * k + 6], row[8 * k + 7]);
+        for (int r = 0; r != kFirOut; ++r) { acc[r] = 0.0f; w[r] = row[r]; }
+#pragma unroll 1
+        for (int it = 0; it != kFirLoop; ++it)
+            FirTaps<0, 16, FMA>::run(acc, w, row - 16 * it, c_tab.taps + 16 * it);
+        FirTaps<0, kTapsUsed - 16 * kFirLoop, FMA>::run(acc, w, row - 16 * kFirLoop, c_tab.taps + 16 * kFirLoop);
+
+        const uint32_t c = ((tb + (uint32_t) o0) >> 3);
+#pragma unroll
+        for (int k = 0; k != kFirOut / 8; ++k) {
+            uint32_t cc = (c + k) & cmask;
+            size_t o = ((size_t) cc * d.np + s) * 8;
+            float4* py = reinterpret_cast<float4*>(d.ring_y + o);
+            float4* px = reinterpret_cast<float4*>(d.ring_x + o);
+            py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
+            py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
+            px[0] = make_float4(row[8 * k + 0], row[8 * k + 1], row[8 * k + 2], row[8 * k + 3]);
+            px[1] = make_float4(row[8 * k + 4], row[8 * k + 5], row[8 * k + 6], row[8 * k + 7]);
+        }
     }
 }
 
@@ -160,8 +196,11 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
     uint32_t span = head + n_new - b0;
     dim3 grid(d.np / kFirStreams, (span + kFirTile - 1) / kFirTile);
     size_t smem = sizeof(float) * kFirStreams * kFirRow;
-    if (fma) fir_kernel<true><<<grid, kFirWarps * 32, smem, s>>>(d, in, stride, n_new, tail, head, invert);
-    else fir_kernel<false><<<grid, kFirWarps * 32, smem, s>>>(d, in, stride, n_new, tail, head, invert);
+    // 16-byte loads need the chunk to start on a ring-chunk boundary and 16-byte aligned rows
+    int aligned = (head % 8 == 0) && (stride % 8 == 0) && (reinterpret_cast<uintptr_t>(in) % 16 == 0) &&
+                  (reinterpret_cast<uintptr_t>(tail) % 16 == 0);
+    if (fma) fir_kernel<true><<<grid, kFirWarps * 32, smem, s>>>(d, in, stride, n_new, tail, head, invert, aligned);
+    else fir_kernel<false><<<grid, kFirWarps * 32, smem, s>>>(d, in, stride, n_new, tail, head, invert, aligned);
 }
 
 // Keep the last kTailLen raw samples of [tail | new chunk] per stream.
