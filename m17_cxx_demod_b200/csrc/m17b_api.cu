@@ -100,7 +100,7 @@ void ev_collect(m17b_ctx* c)
 int run_round(m17b_ctx* c)
 {
     EvPair p{};
-    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 2 * sizeof(unsigned int), c->compute));      // lagging, fix_count
+    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 7 * sizeof(unsigned int), c->compute));      // lagging, fix_count, dec_count[5]
     ev_begin(c, c->compute, CAT_SCAN, p);
     launch_scan(c->d, c->head, c->compute);
     ev_end(c, c->compute, p);
@@ -161,7 +161,7 @@ void free_all(m17b_ctx* c)
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -240,6 +240,7 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.corr_ring, 96 * np * sizeof(float)));
         CK(cudaMalloc(&d.lim_save, 8 * np * sizeof(float)));
         CK(cudaMalloc(&d.fix_list, np * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.dec_list, 5 * np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
         CK(cudaMalloc(&d.fir_snap, (size_t) kTapsUsed * np * sizeof(float)));
         CK(cudaMalloc(&d.llr, 184 * np * sizeof(int16_t)));

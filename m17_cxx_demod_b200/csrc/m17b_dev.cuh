@@ -84,6 +84,7 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned int rec_count;       // records in the ring
     unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
     unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
+    unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
 };
 
 struct DevPtrs {
@@ -93,6 +94,7 @@ struct DevPtrs {
     float* corr_ring;             // [96][Np]
     float* lim_save;              // [8][Np]
     uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
+    uint32_t* dec_list;           // [5][Np] streams with a completed frame, by decode kind (0..3 = Viterbi map, 4 = LICH / none)
     float* sw_samples;            // [30][Np]
     float* fir_snap;              // [149][Np]
     int16_t* llr;                 // [184][Np]

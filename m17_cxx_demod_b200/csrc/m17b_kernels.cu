@@ -293,11 +293,22 @@ void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s)
     scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head);
 }
 
+// Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to
+// whole warps: all lanes of a warp decode the same kind of frame (same Viterbi length and map).
 __global__ void __launch_bounds__(kDecThreads)
 decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
 {
     extern __shared__ uint16_t hist[];                     // [244][128] survivor decisions
-    const uint32_t s = blockIdx.x * kDecThreads + threadIdx.x;
+    uint32_t g = blockIdx.x * kDecThreads + threadIdx.x;
+    uint32_t s = 0xFFFFFFFFu;
+#pragma unroll
+    for (int k = 0; k != 5; ++k) {
+        const uint32_t n = d.ctr->dec_count[k], padded = (n + 31u) & ~31u;
+        if (s == 0xFFFFFFFFu) {
+            if (g < padded) { s = g < n ? d.dec_list[(size_t) k * d.np + g] : 0xFFFFFFFEu; }
+            else g -= padded;
+        }
+    }
     if (s >= d.n_streams) return;
     decode_lane(d, s, hist + threadIdx.x, head, head64);
 }
@@ -351,7 +362,7 @@ void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
 {
     size_t smem = sizeof(uint16_t) * 244 * kDecThreads;
-    decode_kernel<<<d.np / kDecThreads, kDecThreads, smem, s>>>(d, head, head64);
+    decode_kernel<<<(d.np + 5 * 32 + kDecThreads - 1) / kDecThreads, kDecThreads, smem, s>>>(d, head, head64);
 }
 
 // Per-device kernel attributes (dynamic shared memory above 48 KiB).

@@ -1018,6 +1018,17 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
     for (int k = 0; k != kRing; ++k) d.corr_ring[(size_t) k * d.np + e.s] = e.ring[k * RS];
     if (dpos != pos)
         for (int j = (int) (pos & 7); j != 8; ++j) d.lim_save[(size_t) j * d.np + e.s] = e.lim[j * RS];
+    if (z.pending) {
+        // queue the frame by what M17FrameDecoder::operator() will do with it (M17FrameDecoder.h:353-392),
+        // so that decode_kernel's warps each run one kind
+        const int dec_state = (int) (sb[F_DEC * 32] & 0xFF);
+        int kind = 4;
+        if (z.swt == SW_LSF) kind = 0;
+        else if (z.swt == SW_BERT) kind = 3;
+        else if (z.swt == SW_STREAM) { if (dec_state == DEC_STREAM) kind = 1; }
+        else if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) kind = 2;
+        d.dec_list[(size_t) kind * d.np + ctr_add(&d.ctr->dec_count[kind], 1u)] = e.s;
+    }
     if (pos != head) ctr_add(&d.ctr->lagging, 1u);
 }
 

@@ -32,7 +32,7 @@ struct Emu {
     std::vector<uint32_t> st;
     std::vector<float> ring_y, ring_x, corr_ring, lim_save, sw_samples, fir_snap;
     std::vector<int16_t> llr;
-    std::vector<uint32_t> fix_list;
+    std::vector<uint32_t> fix_list, dec_list;
     std::vector<uint8_t> dec_bytes;
     std::vector<m17b_frame> recs;
     Counters ctr{};
@@ -61,13 +61,14 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.corr_ring.assign(kRing * np, 0.f);
     m.lim_save.assign(8 * np, 0.f);
     m.fix_list.assign(np, 0);
+    m.dec_list.assign(5 * np, 0);
     m.sw_samples.assign(30 * np, 0.f);
     m.fir_snap.assign((size_t) kTapsUsed * np, 0.f);
     m.llr.assign(184 * np, 0);
     m.dec_bytes.assign(56 * np, 0);
     m.recs.resize(rec_cap);
     d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
-    d.lim_save = m.lim_save.data(); d.fix_list = m.fix_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
+    d.lim_save = m.lim_save.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
     for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
 }
@@ -77,6 +78,7 @@ void round(Emu& m)
     DevPtrs& d = m.d;
     m.ctr.lagging = 0;
     m.ctr.fix_count = 0;
+    for (int k = 0; k != 5; ++k) m.ctr.dec_count[k] = 0;
     float ring[kRing], lim[8];
     for (uint32_t s = 0; s != d.n_streams; ++s) {
         LaneIo e;
@@ -89,7 +91,8 @@ void round(Emu& m)
         scan_lane(d, e, m.head, true);
     }
     uint16_t hist[244];
-    for (uint32_t s = 0; s != d.n_streams; ++s) decode_lane(d, s, hist, m.head, m.head64);
+    for (int k = 0; k != 5; ++k)
+        for (uint32_t q = 0; q != m.ctr.dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) k * d.np + q], hist, m.head, m.head64);
     for (uint32_t q = 0; q != m.ctr.fix_count; ++q) fixup_lane(d, m.fix_list[q], m.head);
 }
 
