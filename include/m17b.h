@@ -165,6 +165,15 @@ int  m17b_sync(m17b_ctx* ctx);
  * completed them.  *n receives the number written; call again while *n == cap. */
 int  m17b_drain(m17b_ctx* ctx, m17b_frame* out, size_t cap, size_t* n);
 
+/* Pipelined draining.  Every m17b_submit() gets a ticket (1, 2, ...; m17b_ticket() returns the last one
+ * issued).  m17b_drain_upto() waits only until the submit with that ticket has finished on the device --
+ * later submits keep running -- and returns the records appended up to then (same ordering rules as
+ * m17b_drain; a stream that had not reached the end of that submit yet delivers the rest with a later
+ * ticket or with m17b_drain).  The device-to-host transfer runs on the copy stream beside the kernels of
+ * the later submits.  Keep at most 8 submits in flight. */
+unsigned long long m17b_ticket(const m17b_ctx* ctx);
+int  m17b_drain_upto(m17b_ctx* ctx, unsigned long long ticket, m17b_frame* out, size_t cap, size_t* n);
+
 /* Number of frame records currently waiting on the device (after m17b_sync). */
 int  m17b_pending_frames(m17b_ctx* ctx, size_t* n);
 

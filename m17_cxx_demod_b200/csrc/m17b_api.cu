@@ -46,6 +46,13 @@ struct m17b_ctx {
     m17b_profile prof{};
     Counters host_ctr{};
     cudaEvent_t marks[8] = {};
+    // one completion snapshot per submit in flight (m17b_drain_upto waits for one submit only)
+    static constexpr int kSlots = 8;
+    cudaEvent_t done[kSlots] = {};
+    Counters* snap = nullptr;                  // pinned [kSlots]
+    unsigned long long ticket = 0;             // submits issued
+    unsigned long long slot_ticket[kSlots] = {};
+    uint32_t rec_read = 0;                     // record cursor consumed by the host (monotonic, mod 2^32)
 };
 
 namespace {
@@ -124,12 +131,14 @@ int fetch_counters(m17b_ctx* c)
     return M17B_OK;
 }
 
-// Move every record off the device into c->ready (pinned staging).  The device appends records
-// with one atomic counter, so records of one stream are already in chronological order.
-int pull_records(m17b_ctx* c)
+// Move the records [rec_read, cursor) off the device into c->ready (pinned staging) on the copy
+// stream, so that the transfer overlaps kernels of later submits.  The device appends records at
+// cursor % rec_cap with one monotonic atomic cursor, so records of one stream stay chronological.
+int pull_records(m17b_ctx* c, uint32_t cursor)
 {
-    uint32_t n = std::min(c->host_ctr.rec_count, c->d.rec_cap);
+    uint32_t n = cursor - c->rec_read;
     if (n == 0) return M17B_OK;
+    if (n > c->d.rec_cap) n = c->d.rec_cap;                  // overflow: the device counted the rest as dropped
     if (c->ready_off == c->ready_n) c->ready_off = c->ready_n = 0;
     if (c->ready_n + n > c->ready_cap) {
         size_t cap = std::max<size_t>((c->ready_n + n) * 2, 4096);
@@ -141,13 +150,17 @@ int pull_records(m17b_ctx* c)
         c->ready_cap = cap;
     }
     EvPair p{};
-    ev_begin(c, c->compute, CAT_D2H, p);
-    CK(cudaMemcpyAsync(c->ready + c->ready_n, c->d.recs, sizeof(m17b_frame) * n, cudaMemcpyDeviceToHost, c->compute));
-    ev_end(c, c->compute, p);
-    CK(cudaMemsetAsync(&c->d.ctr->rec_count, 0, sizeof(unsigned int), c->compute));
-    CK(cudaStreamSynchronize(c->compute));
+    ev_begin(c, c->copy, CAT_D2H, p);
+    const uint32_t first = c->rec_read & (c->d.rec_cap - 1);
+    const uint32_t n1 = std::min(n, c->d.rec_cap - first);
+    CK(cudaMemcpyAsync(c->ready + c->ready_n, c->d.recs + first, sizeof(m17b_frame) * n1, cudaMemcpyDeviceToHost, c->copy));
+    if (n1 != n)
+        CK(cudaMemcpyAsync(c->ready + c->ready_n + n1, c->d.recs, sizeof(m17b_frame) * (n - n1), cudaMemcpyDeviceToHost, c->copy));
+    ev_end(c, c->copy, p);
+    CK(cudaStreamSynchronize(c->copy));
     c->prof.d2h_bytes += sizeof(m17b_frame) * n;
-    c->host_ctr.rec_count = 0;
+    c->rec_read = cursor;
+    c->d.rec_read = cursor;
     c->ready_n += n;
     return M17B_OK;
 }
@@ -161,6 +174,8 @@ void free_all(m17b_ctx* c)
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
+    for (auto& e : c->done) if (e) cudaEventDestroy(e);
+    if (c->snap) cudaFreeHost(c->snap);
     cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
@@ -232,6 +247,11 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
         d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
                                         : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 2 * (cfg->max_chunk / kMinFrameSpacing + 2), 0x7fffffffull);
+        d.rec_cap = next_pow2(std::max(d.rec_cap, 64u));          // slot = cursor % rec_cap must survive cursor wrap-around
+        d.rec_read = 0;
+        for (auto& e : c->done) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        CK(cudaHostAlloc((void**) &c->snap, sizeof(Counters) * m17b_ctx::kSlots, cudaHostAllocDefault));
+        std::memset(c->snap, 0, sizeof(Counters) * m17b_ctx::kSlots);
         size_t np = d.np;
         size_t ring_bytes = (size_t) d.ring_chunks * np * 8 * sizeof(float);
         CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
@@ -374,6 +394,12 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
         int rc = run_round(c);
         if (rc != M17B_OK) return rc;
     }
+    // completion snapshot of this submit: counters (incl. the record cursor) + an event
+    const int slot = (int) (c->ticket % m17b_ctx::kSlots);
+    CK(cudaMemcpyAsync(&c->snap[slot], c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaEventRecord(c->done[slot], c->compute));
+    c->ticket += 1;
+    c->slot_ticket[slot] = c->ticket;
     return M17B_OK;
 }
 
@@ -398,7 +424,7 @@ int m17b_pending_frames(m17b_ctx* c, size_t* n)
     if (!c || !n) return M17B_EINVAL;
     int rc = m17b_sync(c);
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
-    *n = (c->ready_n - c->ready_off) + std::min(c->host_ctr.rec_count, c->d.rec_cap);
+    *n = (c->ready_n - c->ready_off) + std::min(c->host_ctr.rec_count - c->rec_read, c->d.rec_cap);
     return rc;
 }
 
@@ -408,7 +434,7 @@ int m17b_drain(m17b_ctx* c, m17b_frame* out, size_t cap, size_t* n)
     *n = 0;
     int rc = m17b_sync(c);
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
-    int rc2 = pull_records(c);
+    int rc2 = pull_records(c, c->host_ctr.rec_count);
     if (rc2 != M17B_OK) return rc2;
     size_t k = std::min(cap, c->ready_n - c->ready_off);
     if (k) std::memcpy(out, c->ready + c->ready_off, k * sizeof(m17b_frame));
@@ -416,6 +442,33 @@ int m17b_drain(m17b_ctx* c, m17b_frame* out, size_t cap, size_t* n)
     *n = k;
     c->prof.decode_frames += k;
     return rc;
+}
+
+unsigned long long m17b_ticket(const m17b_ctx* c) { return c ? c->ticket : 0; }
+
+int m17b_drain_upto(m17b_ctx* c, unsigned long long ticket, m17b_frame* out, size_t cap, size_t* n)
+{
+    if (!c || !n || (!out && cap)) return M17B_EINVAL;
+    *n = 0;
+    CK(cudaSetDevice(c->cfg.device));
+    if (c->ready_off == c->ready_n && ticket != 0) {
+        if (ticket > c->ticket) return M17B_EINVAL;
+        // the newest snapshot slot that is not newer than `ticket` and has not been recycled
+        unsigned long long t = ticket;
+        if (c->ticket - t >= (unsigned long long) m17b_ctx::kSlots) t = c->ticket - m17b_ctx::kSlots + 1;
+        const int slot = (int) ((t - 1) % m17b_ctx::kSlots);
+        CK(cudaEventSynchronize(c->done[slot]));
+        const Counters& k = c->snap[slot];
+        if (k.dropped) return M17B_EOVERFLOW;
+        int rc = pull_records(c, k.rec_count);
+        if (rc != M17B_OK) return rc;
+    }
+    size_t k = std::min(cap, c->ready_n - c->ready_off);
+    if (k) std::memcpy(out, c->ready + c->ready_off, k * sizeof(m17b_frame));
+    c->ready_off += k;
+    *n = k;
+    c->prof.decode_frames += k;
+    return M17B_OK;
 }
 
 int m17b_diag_get(m17b_ctx* c, uint32_t stream, m17b_diag* out)

@@ -81,7 +81,7 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned long long golay_fail;
     unsigned long long faults;
     unsigned long long dropped;
-    unsigned int rec_count;       // records in the ring
+    unsigned int rec_count;       // record cursor: records appended so far (monotonic, mod 2^32)
     unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
     unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
     unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
@@ -104,7 +104,8 @@ struct DevPtrs {
     uint32_t n_streams;
     uint32_t np;                  // padded stream count (multiple of 128)
     uint32_t ring_chunks;         // RC, power of two
-    uint32_t rec_cap;
+    uint32_t rec_cap;             // power of two
+    uint32_t rec_read;            // cursor up to which the host has taken the records (at launch time)
 };
 
 __host__ __device__ inline size_t st_index(uint32_t s, int f)

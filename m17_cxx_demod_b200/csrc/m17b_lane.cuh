@@ -822,6 +822,9 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
     uint32_t fl = valid ? sb[F_FLAGS * 32] : 0u;
     bool active = pos != head && !(fl & (FL_PENDING | FL_FIXUP));
     if (pos != head && !active) ctr_add(&d.ctr->lagging, 1u);
+    // a stream that fell so far behind that the sample ring has wrapped over what it still needs
+    // (submits enqueued back to back without m17b_sync and more stops than rounds): must never happen
+    if (head - pos > d.ring_chunks * 8u - 176u) ctr_add(&d.ctr->faults, 1ull);
     const bool loaded = active;
     uint32_t dpos = pos;
     uint32_t gap_r = 0;                                     // position the filter last resumed at
@@ -1185,8 +1188,8 @@ M17B_FN_COLD void emit_record(const DevPtrs& d, uint32_t s, uint32_t* sb, unsign
     sb[F_SEQ * 32] = seq + 1;
     ctr_add(&d.ctr->frames[type], 1ull);
     uint32_t slot = ctr_add(&d.ctr->rec_count, 1u);
-    if (slot >= d.rec_cap) { ctr_add(&d.ctr->dropped, 1ull); return; }
-    m17b_frame* r = d.recs + slot;
+    if (slot - d.rec_read >= d.rec_cap) { ctr_add(&d.ctr->dropped, 1ull); return; }
+    m17b_frame* r = d.recs + (slot & (d.rec_cap - 1));
     r->stream = s; r->seq = seq; r->sample_pos = sample_pos; r->viterbi_cost = cost;
     r->type = (uint8_t) type; r->pad[0] = r->pad[1] = r->pad[2] = 0;
     const uint8_t* b = d.dec_bytes + s;

@@ -79,6 +79,11 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_sync.argtypes = [ctypes.c_void_p]
         lib.m17b_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
         lib.m17b_pending_frames.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_size_t)]
+        lib.m17b_ticket.restype = ctypes.c_ulonglong
+        lib.m17b_ticket.argtypes = [ctypes.c_void_p]
+        lib.m17b_drain_upto.restype = ctypes.c_int
+        lib.m17b_drain_upto.argtypes = [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_void_p, ctypes.c_size_t,
+                                        ctypes.POINTER(ctypes.c_size_t)]
         lib.m17b_destroy.argtypes = [ctypes.c_void_p]
         lib.m17b_destroy.restype = None
         lib.m17b_host_alloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t]
@@ -185,16 +190,41 @@ class Demodulator:
         self._check(self._lib.m17b_sync(self._ctx), "m17b_sync")
         self._keep.clear()
 
+    def _drain(self, ticket) -> np.ndarray:
+        parts = []
+        cap = max(4096, getattr(self, "_drain_cap", 4096))
+        while True:
+            out = np.empty(cap, dtype=FRAME_DTYPE)
+            got = ctypes.c_size_t()
+            if ticket is None:
+                rc = self._lib.m17b_drain(self._ctx, out.ctypes.data_as(ctypes.c_void_p), cap, ctypes.byref(got))
+            else:
+                rc = self._lib.m17b_drain_upto(self._ctx, ctypes.c_ulonglong(ticket), out.ctypes.data_as(ctypes.c_void_p), cap,
+                                               ctypes.byref(got))
+            self._check(rc, "m17b_drain")
+            parts.append(out[:got.value])
+            if got.value < cap:
+                break
+            cap *= 4
+        self._drain_cap = min(max(4096, 2 * sum(len(p) for p in parts)), 1 << 24)
+        return parts[0] if len(parts) == 1 else np.concatenate(parts)
+
     def drain(self) -> np.ndarray:
-        """All frame records decoded so far (chronological within each stream)."""
-        self.sync()
-        n = ctypes.c_size_t()
-        self._check(self._lib.m17b_pending_frames(self._ctx, ctypes.byref(n)), "m17b_pending_frames")
-        out = np.zeros(max(1, n.value), dtype=FRAME_DTYPE)
-        got = ctypes.c_size_t()
-        self._check(self._lib.m17b_drain(self._ctx, out.ctypes.data_as(ctypes.c_void_p), out.shape[0],
-                                         ctypes.byref(got)), "m17b_drain")
-        return out[:got.value]
+        """All frame records decoded so far (chronological within each stream).  Waits for the device."""
+        r = self._drain(None)
+        self._keep.clear()
+        return r
+
+    def ticket(self) -> int:
+        """Ticket of the most recent submit (see drain_upto)."""
+        return int(self._lib.m17b_ticket(self._ctx))
+
+    def drain_upto(self, ticket: int) -> np.ndarray:
+        """Records appended until the submit with `ticket` finished; later submits keep running."""
+        r = self._drain(ticket)
+        if len(self._keep) > 8:
+            del self._keep[:-8]
+        return r
 
     def demodulate(self, samples: np.ndarray, chunk: int | None = None) -> list[np.ndarray]:
         """Feed [n_streams, n] int16 in chunks; return per-stream record arrays."""

@@ -53,7 +53,8 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     d.n_streams = n_streams;
     d.np = (n_streams + 127u) & ~127u;
     d.ring_chunks = next_pow2((max_chunk + kRoundCap + 160 + 16 + 7) / 8);
-    d.rec_cap = (uint32_t) rec_cap;
+    d.rec_cap = next_pow2((uint32_t) rec_cap);
+    d.rec_read = 0;
     size_t np = d.np;
     m.st.assign((np / 32) * NFIELDS * 32, 0);
     m.ring_y.assign((size_t) d.ring_chunks * np * 8, 0.f);
@@ -66,7 +67,7 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.fir_snap.assign((size_t) kTapsUsed * np, 0.f);
     m.llr.assign(184 * np, 0);
     m.dec_bytes.assign(56 * np, 0);
-    m.recs.resize(rec_cap);
+    m.recs.resize(d.rec_cap);
     d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
     d.lim_save = m.lim_save.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
