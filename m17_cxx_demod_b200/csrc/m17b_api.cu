@@ -176,7 +176,7 @@ void free_all(m17b_ctx* c)
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
     for (auto& e : c->done) if (e) cudaEventDestroy(e);
     if (c->snap) cudaFreeHost(c->snap);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -243,7 +243,7 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         // ring must hold one submit plus the lag a stream may keep plus the look-back
         // of the slow filter path / sliding DFT
         uint32_t need = cfg->max_chunk + kRoundCap + 160 + 16;
-        d.ring_chunks = next_pow2((need + 7) / 8);
+        d.ring_lines = next_pow2((need + kLine - 1) / kLine + 1);
         // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
         d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
                                         : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 2 * (cfg->max_chunk / kMinFrameSpacing + 2), 0x7fffffffull);
@@ -253,10 +253,11 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaHostAlloc((void**) &c->snap, sizeof(Counters) * m17b_ctx::kSlots, cudaHostAllocDefault));
         std::memset(c->snap, 0, sizeof(Counters) * m17b_ctx::kSlots);
         size_t np = d.np;
-        size_t ring_bytes = (size_t) d.ring_chunks * np * 8 * sizeof(float);
+        size_t ring_bytes = (size_t) d.ring_lines * np * kLine * sizeof(float);
         CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
         CK(cudaMalloc(&d.ring_y, ring_bytes));
-        CK(cudaMalloc(&d.ring_x, ring_bytes));
+        CK(cudaMalloc(&d.ring_d, ring_bytes));
+        CK(cudaMalloc(&d.ring_x, ring_bytes / 2));
         CK(cudaMalloc(&d.corr_ring, 96 * np * sizeof(float)));
         CK(cudaMalloc(&d.lim_save, 8 * np * sizeof(float)));
         CK(cudaMalloc(&d.fix_list, np * sizeof(uint32_t)));
@@ -268,7 +269,8 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.recs, (size_t) d.rec_cap * sizeof(m17b_frame)));
         CK(cudaMalloc(&d.ctr, sizeof(Counters)));
         CK(cudaMemsetAsync(d.ring_y, 0, ring_bytes, c->compute));
-        CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes, c->compute));
+        CK(cudaMemsetAsync(d.ring_d, 0, ring_bytes, c->compute));
+        CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes / 2, c->compute));
         CK(cudaMemsetAsync(d.corr_ring, 0, 96 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.lim_save, 0, 8 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.sw_samples, 0, 30 * np * sizeof(float), c->compute));
@@ -549,13 +551,14 @@ int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t
     DevPtrs t{};
     t.n_streams = ns;
     t.np = c->d.np;
-    t.ring_chunks = next_pow2((uint32_t) ((n + 7) / 8 + 1));
-    size_t ring_bytes = (size_t) t.ring_chunks * t.np * 8 * sizeof(float);
+    t.ring_lines = next_pow2((uint32_t) ((n + kLine - 1) / kLine + 1));
+    size_t ring_bytes = (size_t) t.ring_lines * t.np * kLine * sizeof(float);
     int16_t *din = nullptr, *dtail = nullptr;
     float *dy = nullptr, *dx = nullptr;
     int rc = [&]() -> int {
         CK(cudaMalloc(&t.ring_y, ring_bytes));
-        CK(cudaMalloc(&t.ring_x, ring_bytes));
+        CK(cudaMalloc(&t.ring_d, ring_bytes));
+        CK(cudaMalloc(&t.ring_x, ring_bytes / 2));
         CK(cudaMalloc(&din, (size_t) ns * n * sizeof(int16_t)));
         CK(cudaMalloc(&dtail, (size_t) ns * kTailLen * sizeof(int16_t)));
         CK(cudaMalloc(&dy, (size_t) ns * n * sizeof(float)));
@@ -572,7 +575,7 @@ int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t
         CK(cudaStreamSynchronize(c->compute));
         return M17B_OK;
     }();
-    cudaFree(t.ring_y); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx);
+    cudaFree(t.ring_y); cudaFree(t.ring_d); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx);
     return rc;
 }
 

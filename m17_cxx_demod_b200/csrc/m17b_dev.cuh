@@ -2,12 +2,20 @@
 //
 // Data layout in HBM (N = streams padded to a multiple of 128, "Np"):
 //
-//   sample ring   ring_y / ring_x : float [RC chunks][Np][8]
-//       chunk c of stream s holds samples 8c .. 8c+7 (32 B = one DRAM sector).
-//       ring_x = the scaled input (apps/m17-demod.cpp:489), ring_y = matched
-//       filter output computed speculatively for every sample.  A warp of 32
-//       consecutive streams reads/writes 1 KiB contiguous per chunk, and a lane
-//       that runs ahead of / behind its neighbours still moves whole sectors.
+//   sample ring   ring_y / ring_d : float [RL lines][Np][32]
+//       line l of stream s holds samples 32l .. 32l+31 (128 B = one L2 line, four
+//       32-byte sectors).  ring_y = matched filter output computed speculatively
+//       for every sample; ring_d = x[n] - x[n-120], the input of the carrier
+//       detect's sliding DFT (SlidingDFT.h:123-124), where x is the scaled input
+//       (apps/m17-demod.cpp:489).  The lanes of a scan warp sit at different
+//       stream positions (each stops at its own frame completions), so a lane must
+//       own whole lines: it consumes the four sectors of a line in four consecutive
+//       8-sample blocks (one DRAM fetch, three L2 hits).  With 8-sample lines
+//       interleaved over streams (the first layout) every sector read dragged in
+//       three neighbours' sectors that were evicted before their lanes got there:
+//       3.6x the algorithmic DRAM traffic (profiles/r01b_*).
+//                 ring_x : int16 [RL][Np][32]  raw (sign-corrected) input, only for the
+//       rare paths that rebuild filter history after a carrier-detect gap.
 //   per-stream scalars            : uint32 [Np/32][NFIELDS][32]   (one coalesced
 //       128 B line per field per warp)
 //   correlator ring               : float [96][Np]    (Correlator::buffer_ + one block of look-ahead)
@@ -28,7 +36,8 @@ namespace m17b {
 constexpr int kTaps = 150;            // M17Demodulator.h:79-118 (tap 149 is 0.0)
 constexpr int kTapsUsed = 149;
 constexpr int kTailLen = 160;         // raw history kept between submits (>= 148 + 7)
-constexpr int kChunk = 8;             // samples per ring chunk
+constexpr int kChunk = 8;             // samples per scan block (one 32-byte sector)
+constexpr int kLine = 32;             // samples per ring line (128 bytes of float)
 constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:149: 48000/400)
 constexpr int kRoundCap = 2048;       // samples a stream may advance per scan launch
 constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
@@ -89,8 +98,9 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
 
 struct DevPtrs {
     uint32_t* st;                 // [Np/32][NFIELDS][32]
-    float* ring_y;                // [RC][Np][8]
-    float* ring_x;
+    float* ring_y;                // [RL][Np][32]
+    float* ring_d;                // [RL][Np][32]
+    int16_t* ring_x;              // [RL][Np][32]
     float* corr_ring;             // [96][Np]
     float* lim_save;              // [8][Np]
     uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
@@ -103,7 +113,7 @@ struct DevPtrs {
     Counters* ctr;
     uint32_t n_streams;
     uint32_t np;                  // padded stream count (multiple of 128)
-    uint32_t ring_chunks;         // RC, power of two
+    uint32_t ring_lines;          // RL, power of two
     uint32_t rec_cap;             // power of two
     uint32_t rec_read;            // cursor up to which the host has taken the records (at launch time)
 };

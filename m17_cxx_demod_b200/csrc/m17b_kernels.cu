@@ -160,7 +160,7 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
     __syncthreads();
 
     const uint32_t s = s0 + lane;
-    const uint32_t cmask = d.ring_chunks - 1;
+    const uint32_t lmask = d.ring_lines - 1;
 #pragma unroll 1
     for (int pass = 0; pass != kFirPasses; ++pass) {
         const int o0 = pass * kFirPass + warp * kFirOut;              // first output of this thread in the tile
@@ -174,17 +174,30 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
             FirTaps<0, 16, FMA>::run(acc, w, row - 16 * it, c_tab.taps + 16 * it);
         FirTaps<0, kTapsUsed - 16 * kFirLoop, FMA>::run(acc, w, row - 16 * kFirLoop, c_tab.taps + 16 * kFirLoop);
 
-        const uint32_t c = ((tb + (uint32_t) o0) >> 3);
+        // 16 outputs = two 8-sample blocks; a block never straddles a 32-sample ring line.  Besides y:
+        // d = x[n] - x[n-120] (the sliding DFT's `sample - oldest`, SlidingDFT.h:123-124; the 160-sample
+        // halo covers the look-back) and the raw sample as int16 (exact inverse of the scaling).
 #pragma unroll
         for (int k = 0; k != kFirOut / 8; ++k) {
-            uint32_t cc = (c + k) & cmask;
-            size_t o = ((size_t) cc * d.np + s) * 8;
+            const uint32_t p = tb + (uint32_t) o0 + 8u * k;
+            const size_t o = ((size_t) ((p >> 5) & lmask) * d.np + s) * kLine + (p & (kLine - 1));
             float4* py = reinterpret_cast<float4*>(d.ring_y + o);
-            float4* px = reinterpret_cast<float4*>(d.ring_x + o);
+            float4* pd = reinterpret_cast<float4*>(d.ring_d + o);
             py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
             py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
-            px[0] = make_float4(row[8 * k + 0], row[8 * k + 1], row[8 * k + 2], row[8 * k + 3]);
-            px[1] = make_float4(row[8 * k + 4], row[8 * k + 5], row[8 * k + 6], row[8 * k + 7]);
+            float dl[8];
+            uint32_t raw[4];
+#pragma unroll
+            for (int i = 0; i != 8; ++i) dl[i] = __fsub_rn(row[8 * k + i], row[8 * k + i - kDftN]);
+#pragma unroll
+            for (int i = 0; i != 4; ++i) {
+                int lo = __float2int_rn(__fmul_rn(row[8 * k + 2 * i], 41067.0f));
+                int hi = __float2int_rn(__fmul_rn(row[8 * k + 2 * i + 1], 41067.0f));
+                raw[i] = ((uint32_t) lo & 0xFFFFu) | ((uint32_t) hi << 16);
+            }
+            pd[0] = make_float4(dl[0], dl[1], dl[2], dl[3]);
+            pd[1] = make_float4(dl[4], dl[5], dl[6], dl[7]);
+            *reinterpret_cast<uint4*>(d.ring_x + o) = make_uint4(raw[0], raw[1], raw[2], raw[3]);
         }
     }
 }
@@ -230,9 +243,9 @@ __global__ void gather_ring_kernel(DevPtrs d, uint32_t n, float* __restrict__ y,
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t s = blockIdx.y;
     if (i >= n || s >= d.n_streams) return;
-    size_t o = ((size_t) ((i >> 3) & (d.ring_chunks - 1)) * d.np + s) * 8 + (i & 7);
+    size_t o = ((size_t) ((i >> 5) & (d.ring_lines - 1)) * d.np + s) * kLine + (i & (kLine - 1));
     y[(size_t) s * n + i] = d.ring_y[o];
-    if (x) x[(size_t) s * n + i] = d.ring_x[o];
+    if (x) x[(size_t) s * n + i] = scale_sample(d.ring_x[o]);
 }
 
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s)
@@ -281,9 +294,10 @@ scan_kernel(DevPtrs d, uint32_t head)
     e.llr = d.llr + s;
     e.snap = d.fir_snap + s;
     e.ring_y = d.ring_y;
+    e.ring_d = d.ring_d;
     e.ring_x = d.ring_x;
     e.np = d.np;
-    e.cmask = d.ring_chunks - 1;
+    e.lmask = d.ring_lines - 1;
     e.s = s;
     scan_lane(d, e, head, s < d.n_streams);
 }
@@ -324,7 +338,7 @@ fixup_kernel(DevPtrs d, uint32_t head)
 {
     __shared__ float xs[kTapsUsed], snap[kTapsUsed];
     const uint32_t n_req = d.ctr->fix_count;
-    const uint32_t cmask = d.ring_chunks - 1;
+    const uint32_t cmask = d.ring_lines - 1;
     const int t = threadIdx.x;
     for (uint32_t q = blockIdx.x; q < n_req; q += gridDim.x) {
         const uint32_t s = d.fix_list[q];
@@ -335,7 +349,7 @@ fixup_kernel(DevPtrs d, uint32_t head)
         const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
         if (t < kTapsUsed) {
             snap[t] = d.fir_snap[(size_t) t * d.np + s];
-            xs[t] = t < upto ? d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)] : 0.f;
+            xs[t] = t < upto ? scale_i16(d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)]) : 0.f;
         }
         __syncthreads();
         if (t >= done && t < upto) {

@@ -322,22 +322,38 @@ M17B_FN_COLD F2 clock_update_index(uint32_t* sb, int ssi, uint32_t ck_count)
     return r;
 }
 
-M17B_FN size_t ring_off(uint32_t p, uint32_t cmask, uint32_t np, uint32_t s)
+M17B_FN size_t ring_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
 {
-    return ((size_t) ((p >> 3) & cmask) * np + s) * 8 + (p & 7);
+    return ((size_t) ((p >> 5) & lmask) * np + s) * kLine + (p & (kLine - 1));
 }
+
+// apps/m17-demod.cpp:489: float(double(sample) / 41067.0)
+#ifdef __CUDACC__
+M17B_FN float scale_i16(int v)
+{
+    // q = s*r, one Newton correction with two FMAs gives the correctly rounded float quotient, which
+    // equals the reference's double-rounded value for all 65536 inputs (tests/test_gpu_parity.py)
+    const float r = 0x1.988864p-16f;       // RN(1 / 41067)
+    float sf = (float) v;
+    float q = __fmul_rn(sf, r);
+    float e = __fmaf_rn(-q, 41067.0f, sf);
+    return __fmaf_rn(e, r, q);
+}
+#else
+M17B_FN float scale_i16(int v) { return (float) ((double) v / 41067.0); }
+#endif
 
 // FIR history snapshot when the carrier detect gates the filter off
 // (M17Demodulator.h:675-689: demod_filter is not clocked while !dcd_).  snap[j] =
 // the j-th most recent input the filter has seen; k = samples clocked since the
 // last resume (>= 149 unless the carrier dropped again at once).
-M17B_FN_COLD void take_snapshot(float* snap, const float* ring_x, uint32_t np, uint32_t cmask,
+M17B_FN_COLD void take_snapshot(float* snap, const int16_t* ring_x, uint32_t np, uint32_t lmask,
                                 uint32_t s, uint32_t pos, int k)
 {
     if (k < kTapsUsed)
         for (int j = kTapsUsed - 1; j >= k; --j) snap[(size_t) j * np] = snap[(size_t) (j - k) * np];
     int n = k < kTapsUsed ? k : kTapsUsed;
-    for (int j = 0; j != n; ++j) snap[(size_t) j * np] = ring_x[ring_off(pos - (uint32_t) j, cmask, np, s)];
+    for (int j = 0; j != n; ++j) snap[(size_t) j * np] = scale_i16(ring_x[ring_off(pos - (uint32_t) j, lmask, np, s)]);
 }
 
 // Util.h:128-145 (llr<float,4>) -> packed (second << 8 | first) int8 pair.  The reference
@@ -391,8 +407,9 @@ struct LaneIo {
     int16_t* llr;          // + s, stride np
     float* snap;           // + s, stride np
     const float* ring_y;
-    const float* ring_x;
-    uint32_t np, cmask, s;
+    const float* ring_d;
+    const int16_t* ring_x;
+    uint32_t np, lmask, s;
 };
 
 #define M17B_UPDATE_VALUES(index_)                                                  \
@@ -768,7 +785,17 @@ M17B_FN void event_step(Scan& z, const LaneIo& e)
     }
 }
 
-struct Chunk { float y[8], x[8], o[8]; };
+struct Chunk { float y[8], d[8]; };      // one block of ring_y / ring_d
+
+M17B_FN void load_chunk(Chunk& c, const LaneIo& e, uint32_t base)
+{
+    const size_t o = ring_off(base, e.lmask, e.np, e.s);
+    const float4* py = reinterpret_cast<const float4*>(e.ring_y + o);
+    const float4* pd = reinterpret_cast<const float4*>(e.ring_d + o);
+    float4 a0 = py[0], a1 = py[1], b0 = pd[0], b1 = pd[1];
+    c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
+    c.d[0] = b0.x; c.d[1] = b0.y; c.d[2] = b0.z; c.d[3] = b0.w; c.d[4] = b1.x; c.d[5] = b1.y; c.d[6] = b1.z; c.d[7] = b1.w;
+}
 
 // Dense pass over samples [jb, je) of the block starting at absolute position `base`.
 M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base,
@@ -778,7 +805,7 @@ M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int j
     for (int j = 0; j != 8; ++j) {
         if (j < jb || j >= je) continue;
         {   // dcd(input): SlidingDFT.h:118-132, DataCarrierDetect.h:53-58
-            float delta = c.x[j] - c.o[j];
+            float delta = c.d[j];           // sample - oldest, formed by fir_kernel
             float a = z.re0 + delta, b = z.im0;
             z.re0 = a * c0r - b * c0i; z.im0 = a * c0i + b * c0r;
             a = z.re1 + delta; b = z.im1;
@@ -824,7 +851,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
     if (pos != head && !active) ctr_add(&d.ctr->lagging, 1u);
     // a stream that fell so far behind that the sample ring has wrapped over what it still needs
     // (submits enqueued back to back without m17b_sync and more stops than rounds): must never happen
-    if (head - pos > d.ring_chunks * 8u - 176u) ctr_add(&d.ctr->faults, 1ull);
+    if (head - pos > d.ring_lines * (uint32_t) kLine - 176u) ctr_add(&d.ctr->faults, 1ull);
     const bool loaded = active;
     uint32_t dpos = pos;
     uint32_t gap_r = 0;                                     // position the filter last resumed at
@@ -865,6 +892,9 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
 
     const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
     int budget = kRoundCap;
+    Chunk pf;                                               // prefetched block
+    uint32_t pf_base = 1u;                                  // never a block start: nothing prefetched yet
+    memset(&pf, 0, sizeof(pf));
 
     while (warp_any(active)) {
         uint32_t base = 0;
@@ -893,15 +923,12 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
                 }
             }
             if (go && jb_d < je) {
+                // this block's samples were requested one iteration ago (the lane's next 32-byte sector of
+                // its own ring line); request the next block's before the arithmetic of this one
                 Chunk c;
-                const uint32_t cc = base >> 3;
-                const float4* py = reinterpret_cast<const float4*>(e.ring_y + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
-                const float4* px = reinterpret_cast<const float4*>(e.ring_x + ((size_t) (cc & e.cmask) * e.np + e.s) * 8);
-                const float4* po = reinterpret_cast<const float4*>(e.ring_x + ((size_t) ((cc - 15) & e.cmask) * e.np + e.s) * 8);
-                float4 a0 = py[0], a1 = py[1], b0 = px[0], b1 = px[1], o0 = po[0], o1 = po[1];
-                c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
-                c.x[0] = b0.x; c.x[1] = b0.y; c.x[2] = b0.z; c.x[3] = b0.w; c.x[4] = b1.x; c.x[5] = b1.y; c.x[6] = b1.z; c.x[7] = b1.w;
-                c.o[0] = o0.x; c.o[1] = o0.y; c.o[2] = o0.z; c.o[3] = o0.w; c.o[4] = o1.x; c.o[5] = o1.y; c.o[6] = o1.z; c.o[7] = o1.w;
+                if (pf_base == base) c = pf; else load_chunk(c, e, base);
+                pf_base = base + 8u;
+                load_chunk(pf, e, pf_base);
                 dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
                 const int n = je - jb_d;
                 if (initializing) z.init -= n;              // count_ stays 0 while initializing
@@ -971,7 +998,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
                 if (initializing) {
                     if (z.init == 0) {                      // from the next sample on the filter is gated by !dcd_
                         z.gap_k = kTapsUsed;
-                        take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, kTapsUsed);
+                        take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, kTapsUsed);
                     }
                 } else if (!z.dcd) {
                     if (z.count == 384) {                   // :675-689
@@ -984,7 +1011,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
                     update_dcd(z, e);
                     z.count = 0;
                     dcd_update(z);
-                    if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.cmask, e.s, pos - 1, z.gap_k);
+                    if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, z.gap_k);
                 }
             }
             active = pos != head && !z.pending && budget > 0;
@@ -1059,9 +1086,9 @@ M17B_FN void fixup_lane(const DevPtrs& d, uint32_t s, uint32_t head)
     const int done = (int) sb[F_GAPDONE * 32];
     uint32_t avail = head - R;
     const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
-    const uint32_t cmask = d.ring_chunks - 1;
+    const uint32_t lmask = d.ring_lines - 1;
     float xs[kTapsUsed];
-    for (int m = 0; m < upto; ++m) xs[m] = d.ring_x[ring_off(R + (uint32_t) m, cmask, d.np, s)];
+    for (int m = 0; m < upto; ++m) xs[m] = scale_i16(d.ring_x[ring_off(R + (uint32_t) m, lmask, d.np, s)]);
     for (int k = done; k < upto; ++k) {
         float y;
         {
@@ -1072,7 +1099,7 @@ M17B_FN void fixup_lane(const DevPtrs& d, uint32_t s, uint32_t head)
             }
             y = result;
         }
-        d.ring_y[ring_off(R + (uint32_t) k, cmask, d.np, s)] = y;
+        d.ring_y[ring_off(R + (uint32_t) k, lmask, d.np, s)] = y;
     }
     sb[F_GAPDONE * 32] = (uint32_t) upto;
     sb[F_FLAGS * 32] &= ~FL_FIXUP;

@@ -30,8 +30,8 @@ uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p
 struct Emu {
     DevPtrs d{};
     std::vector<uint32_t> st;
-    std::vector<float> ring_y, ring_x, corr_ring, lim_save, sw_samples, fir_snap;
-    std::vector<int16_t> llr;
+    std::vector<float> ring_y, ring_d, corr_ring, lim_save, sw_samples, fir_snap;
+    std::vector<int16_t> llr, ring_x;
     std::vector<uint32_t> fix_list, dec_list;
     std::vector<uint8_t> dec_bytes;
     std::vector<m17b_frame> recs;
@@ -52,13 +52,14 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     DevPtrs& d = m.d;
     d.n_streams = n_streams;
     d.np = (n_streams + 127u) & ~127u;
-    d.ring_chunks = next_pow2((max_chunk + kRoundCap + 160 + 16 + 7) / 8);
+    d.ring_lines = next_pow2((max_chunk + kRoundCap + 160 + 16 + kLine - 1) / kLine + 1);
     d.rec_cap = next_pow2((uint32_t) rec_cap);
     d.rec_read = 0;
     size_t np = d.np;
     m.st.assign((np / 32) * NFIELDS * 32, 0);
-    m.ring_y.assign((size_t) d.ring_chunks * np * 8, 0.f);
-    m.ring_x.assign((size_t) d.ring_chunks * np * 8, 0.f);
+    m.ring_y.assign((size_t) d.ring_lines * np * kLine, 0.f);
+    m.ring_d.assign((size_t) d.ring_lines * np * kLine, 0.f);
+    m.ring_x.assign((size_t) d.ring_lines * np * kLine, 0);
     m.corr_ring.assign(kRing * np, 0.f);
     m.lim_save.assign(8 * np, 0.f);
     m.fix_list.assign(np, 0);
@@ -68,7 +69,7 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.llr.assign(184 * np, 0);
     m.dec_bytes.assign(56 * np, 0);
     m.recs.resize(d.rec_cap);
-    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
+    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
     d.lim_save = m.lim_save.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
     for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
@@ -87,8 +88,8 @@ void round(Emu& m)
         e.sb = d.st + st_index(s, 0);
         e.ring = ring; e.lim = lim; e.ring_base = ring; e.lim_base = lim; e.col = 0;
         e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
-        e.ring_y = d.ring_y; e.ring_x = d.ring_x;
-        e.np = d.np; e.cmask = d.ring_chunks - 1; e.s = s;
+        e.ring_y = d.ring_y; e.ring_d = d.ring_d; e.ring_x = d.ring_x;
+        e.np = d.np; e.lmask = d.ring_lines - 1; e.s = s;
         scan_lane(d, e, m.head, true);
     }
     uint16_t hist[244];
@@ -133,9 +134,13 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
         uint32_t c = (uint32_t) std::min<size_t>(chunk_sizes[ci++ % n_chunk_sizes], n - off);
         for (size_t s = 0; s != n_streams; ++s)
             for (uint32_t i = 0; i != c; ++i) {
-                size_t o = ring_off(m.head + i, d.ring_chunks - 1, d.np, (uint32_t) s);
-                m.ring_y[o] = y[s * n + off + i];
-                m.ring_x[o] = x[s * n + off + i];
+                size_t o = ring_off(m.head + i, d.ring_lines - 1, d.np, (uint32_t) s);
+                size_t t = off + i;
+                int v = samples[s * stride + t];
+                if (invert) v = (int) (int16_t) (-v);
+                m.ring_y[o] = y[s * n + t];
+                m.ring_d[o] = x[s * n + t] - (t >= (size_t) kDftN ? x[s * n + t - kDftN] : 0.f);
+                m.ring_x[o] = (int16_t) v;
             }
         m.head += c; m.head64 += c; off += c;
         int rounds = (int) (c / kMinFrameSpacing) + 2;
