@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--chunk", type=int, default=9600, help="samples per channel per step")
     ap.add_argument("--unique", type=int, default=1024, help="unique waveforms tiled over the channels")
     ap.add_argument("--fma", action="store_true", help="fused multiply-add matched filter (not bit-identical)")
-    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
@@ -210,6 +210,7 @@ def main():
     rec_cap = min(channels * 2 * (T // 1600 + 2) * 3, 2**31 - 1)          # two steps in flight
     d = m.Demodulator(channels, T, flags=flags, device=local, frame_capacity=rec_cap)
     fp32_peak = d.measure_fp32_peak(1)
+    mix_scalar, mix_packed = d.measure_fp32_peak(2), d.measure_fp32_peak(4)
 
     def barrier():
         torch.cuda.synchronize()
@@ -282,7 +283,13 @@ def main():
         "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
                      "peak_source": "measured here: packed FFMA microkernel (m17b_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
-                     "alg_flop_per_sample": ALG_FLOP_PER_SAMPLE, "avg_launch_ms": fir_ms_per_launch},
+                     "alg_flop_per_sample": ALG_FLOP_PER_SAMPLE, "avg_launch_ms": fir_ms_per_launch,
+                     # the bit-identical filter must round the product and the sum separately: a multiply and an
+                     # add per tap instead of one FFMA, i.e. at most half the FFMA-counted peak.  Measured here
+                     # with the same instruction mix (FMUL+FADD, and 2 FMUL + 1 packed FADD2 as the kernel issues).
+                     "exact_mode_ceiling": None if args.fma else {
+                         "fmul_fadd_tflops": mix_scalar, "fmul_fadd2_tflops": mix_packed,
+                         "frac_of_ceiling": achieved / max(mix_scalar, mix_packed) if max(mix_scalar, mix_packed) > 0 else None}},
         "kernel_share": {k: v / ksum for k, v in kernel_ms.items()},
         "kernel_ms_per_step": {k: v / K for k, v in kernel_ms.items()},
         "gpu_launches": launches,
@@ -312,41 +319,60 @@ def main():
     del d
     # ---- e2e: same call sequence from pinned host memory --------------------------------------
     if not args.no_e2e:
-        Ke = max(1, min(args.e2e_steps, K))
-        de = m.Demodulator(channels, T, flags=0, device=local)
-        bufs = [m.demod.PinnedBuffer((channels, T)) for _ in range(Ke + 1)]
+        Ke = max(1, args.e2e_steps if world == 1 else min(args.e2e_steps, 4))   # bounds pinned host memory per rank
+        NW = 2                                                 # untimed warm-up submits (one per staging buffer)
+        if (Ke + NW) * T > total:
+            Ke = total // T - NW
+        DEPTH = 2                                              # submits enqueued ahead of the record read-back
+        de = m.Demodulator(channels, T, flags=m.PROFILE, device=local,
+                           frame_capacity=min(channels * (DEPTH + 2) * (T // 1600 + 2) * 3, 2**31 - 1))
+        bufs = [m.demod.PinnedBuffer((channels, T)) for _ in range(Ke + NW)]
         idx_h = (np.arange(lo, hi) % U)
         for k, b in enumerate(bufs):
             np.take(uniq[:, k * T:(k + 1) * T], idx_h, axis=0, out=b.array)
-        de.submit(bufs[0].array)
-        de.drain()
+        for k in range(NW):
+            de.submit(bufs[k].array)
+            de.drain()
+        de.profile(reset=True)
         barrier()
         t0 = time.perf_counter()
+        marks = []
         d2h = 0
         fr = 0
-        # submit k+1 is enqueued before the records of step k are read back, so the copy of the
-        # next chunk overlaps the kernels of the current one (double-buffered staging)
-        de.submit(bufs[1].array)
-        prev = de.ticket()
-        for k in range(1, Ke + 1):
-            if k + 1 <= Ke:
-                de.submit(bufs[k + 1].array)
-                nxt = de.ticket()
-                r = de.drain_upto(prev)
-                prev = nxt
-            else:
-                r = de.drain()
+        # Every step: one m17b_submit from pinned host memory (H2D on the copy stream into one of two
+        # staging buffers, kernels on the compute stream) and one read-back of that step's frame records
+        # (D2H on its own stream).  Submits are enqueued DEPTH steps ahead of the read-back, so the upload
+        # of chunk k+2 runs under the kernels of chunk k+1 and the read-back of chunk k.
+        tickets = []
+        for k in range(NW, Ke + NW):
+            de.submit(bufs[k].array)
+            tickets.append(de.ticket())
+            if len(tickets) > DEPTH:
+                r = de.drain_upto(tickets.pop(0))
+                marks.append(time.perf_counter())
+                d2h += r.nbytes
+                fr += len(r)
+        while tickets:
+            t_k = tickets.pop(0)
+            r = de.drain_upto(t_k) if tickets else de.drain()
+            marks.append(time.perf_counter())
             d2h += r.nbytes
             fr += len(r)
         barrier()
         te = time.perf_counter() - t0
+        prof_e = de.profile()
         tt = torch.tensor([te], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         te = float(tt.item())
         line["e2e"] = {"value": world * channels * Ke * T / te / 1e6, "unit": "Msamples/s",
                        "h2d_bytes_per_step": channels * T * 2, "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
-                       "frames_per_s": world * fr / te}
+                       "frames_per_s": world * fr / te, "pipeline_depth": DEPTH,
+                       "ms_between_drains": [round(1e3 * (b - a), 2) for a, b in zip([t0] + marks[:-1], marks)],
+                       "kernel_ms_per_step": {"fir": prof_e.fir_ms / Ke, "scan": prof_e.scan_ms / Ke,
+                                              "decode": prof_e.decode_ms / Ke, "h2d": prof_e.h2d_ms / Ke},
+                       "h2d_gbs": (prof_e.h2d_bytes / (prof_e.h2d_ms * 1e-3) / 1e9) if prof_e.h2d_ms else None,
+                       "timing": "host clock around Ke submit+drain pairs incl. pipeline fill and final drain"}
         for b in bufs:
             b.free()
         del de

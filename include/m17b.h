@@ -194,7 +194,8 @@ int  m17b_debug_filter(m17b_ctx* ctx, const int16_t* samples_host, size_t n, siz
 
 /* FP32 pipe microbenchmark: sustained FFMA throughput of the context's GPU in TFLOP/s
  * (2 flop per FMA), the denominator of the matched filter's roofline fraction.
- * variant 0: scalar FFMA; 1: packed fma.rn.f32x2; 2: FMUL+FADD pairs. */
+ * variant 0: scalar FFMA; 1: packed fma.rn.f32x2; 2: FMUL+FADD pairs;
+ * 3: register-operand FFMA; 4: two FMUL + one packed FADD2 (the exact-mode filter mix). */
 int  m17b_measure_fp32_peak(m17b_ctx* ctx, int variant, double* tflops);
 
 #ifdef __cplusplus

@@ -32,7 +32,7 @@ struct m17b_ctx {
     int16_t* stage[2] = {nullptr, nullptr};
     cudaEvent_t stage_free[2] = {nullptr, nullptr}, stage_ready[2] = {nullptr, nullptr};
     int cur_stage = 0;
-    cudaStream_t compute = nullptr, copy = nullptr;
+    cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;   // kernels; sample H2D; record D2H
     uint32_t head = 0;
     unsigned long long head64 = 0;
     int sm_count = 0;
@@ -150,14 +150,15 @@ int pull_records(m17b_ctx* c, uint32_t cursor)
         c->ready_cap = cap;
     }
     EvPair p{};
-    ev_begin(c, c->copy, CAT_D2H, p);
+    // own stream: a record read-back never queues behind the next submit's sample upload
+    ev_begin(c, c->d2h, CAT_D2H, p);
     const uint32_t first = c->rec_read & (c->d.rec_cap - 1);
     const uint32_t n1 = std::min(n, c->d.rec_cap - first);
-    CK(cudaMemcpyAsync(c->ready + c->ready_n, c->d.recs + first, sizeof(m17b_frame) * n1, cudaMemcpyDeviceToHost, c->copy));
+    CK(cudaMemcpyAsync(c->ready + c->ready_n, c->d.recs + first, sizeof(m17b_frame) * n1, cudaMemcpyDeviceToHost, c->d2h));
     if (n1 != n)
-        CK(cudaMemcpyAsync(c->ready + c->ready_n + n1, c->d.recs, sizeof(m17b_frame) * (n - n1), cudaMemcpyDeviceToHost, c->copy));
-    ev_end(c, c->copy, p);
-    CK(cudaStreamSynchronize(c->copy));
+        CK(cudaMemcpyAsync(c->ready + c->ready_n + n1, c->d.recs, sizeof(m17b_frame) * (n - n1), cudaMemcpyDeviceToHost, c->d2h));
+    ev_end(c, c->d2h, p);
+    CK(cudaStreamSynchronize(c->d2h));
     c->prof.d2h_bytes += sizeof(m17b_frame) * n;
     c->rec_read = cursor;
     c->d.rec_read = cursor;
@@ -171,6 +172,7 @@ void free_all(m17b_ctx* c)
     cudaSetDevice(c->cfg.device);
     if (c->compute) cudaStreamSynchronize(c->compute);
     if (c->copy) cudaStreamSynchronize(c->copy);
+    if (c->d2h) cudaStreamSynchronize(c->d2h);
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
@@ -187,6 +189,7 @@ void free_all(m17b_ctx* c)
     }
     if (c->compute) cudaStreamDestroy(c->compute);
     if (c->copy) cudaStreamDestroy(c->copy);
+    if (c->d2h) cudaStreamDestroy(c->d2h);
     delete c;
 }
 
@@ -236,6 +239,7 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         c->sm_count = prop.multiProcessorCount;
         CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
 
         DevPtrs& d = c->d;
         d.n_streams = cfg->n_streams;
@@ -352,8 +356,11 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
         if (!c->stage[b]) CK(cudaMalloc(&c->stage[b], (size_t) ns * c->cfg.max_chunk * sizeof(int16_t)));
         CK(cudaStreamWaitEvent(c->copy, c->stage_free[b], 0));       // kernels of two submits ago are done with it
         ev_begin(c, c->copy, CAT_H2D, p);
-        CK(cudaMemcpy2DAsync(c->stage[b], n * sizeof(int16_t), samples, stride * sizeof(int16_t),
-                             n * sizeof(int16_t), ns, cudaMemcpyHostToDevice, c->copy));
+        if (stride == n)      // contiguous [N][n]: one linear copy (full PCIe rate, no per-row descriptors)
+            CK(cudaMemcpyAsync(c->stage[b], samples, (size_t) ns * n * sizeof(int16_t), cudaMemcpyHostToDevice, c->copy));
+        else
+            CK(cudaMemcpy2DAsync(c->stage[b], n * sizeof(int16_t), samples, stride * sizeof(int16_t),
+                                 n * sizeof(int16_t), ns, cudaMemcpyHostToDevice, c->copy));
         ev_end(c, c->copy, p);
         CK(cudaEventRecord(c->stage_ready[b], c->copy));
         CK(cudaStreamWaitEvent(c->compute, c->stage_ready[b], 0));

@@ -92,18 +92,41 @@ constexpr int kFirCols = kFirTile + kFirHalo;      // 416 staged samples per str
 constexpr int kFirRow = kFirCols + 1;              // 417: odd stride -> conflict-free columns
 constexpr int kFirLoop = 9;                        // taps 0..143 in a rolled loop of 16, 144..148 unrolled
 
-// One tap for 16 consecutive outputs held in acc[]; w[] is a 16-entry register window: slot
+// Two accumulators in one 64-bit register pair.  Exact mode adds two separately rounded products
+// with one packed FADD2 (add.rn.f32x2): half the issue slots of two FADDs, same rounding per half.
+// (A packed mul.rn.f32x2 feeding it is NOT used: ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2
+// into FFMA2 even under --fmad=false, which would change the rounding.)
+struct Acc2 { unsigned long long v; };
+
+__device__ __forceinline__ void acc2_add(Acc2& a, float p0, float p1)
+{
+    unsigned long long p;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(p) : "f"(p0), "f"(p1));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(a.v) : "l"(a.v), "l"(p));
+}
+
+__device__ __forceinline__ void acc2_fma(Acc2& a, float x0, float x1, float tap)
+{
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+    lo = __fmaf_rn(x0, tap, lo);
+    hi = __fmaf_rn(x1, tap, hi);
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a.v) : "f"(lo), "f"(hi));
+}
+
+// One tap for 16 consecutive outputs held in acc[] (pairs); w[] is a 16-entry register window: slot
 // (k & 15) holds sample t0 + k.  Tap index I = 16 * it + K; rowp = row - 16 * it.
 template <int K, int KEND, bool FMA>
 struct FirTaps {
-    __device__ __forceinline__ static void run(float (&acc)[kFirOut], float (&w)[kFirOut], const float* rowp, const float* tp)
+    __device__ __forceinline__ static void run(Acc2 (&acc)[kFirOut / 2], float (&w)[kFirOut], const float* rowp, const float* tp)
     {
         w[(16 - K) & 15] = rowp[-K];               // sample t0 - I replaces t0 + 16 - I
         const float tap = tp[K];
 #pragma unroll
-        for (int r = 0; r != kFirOut; ++r) {
-            float x = w[(r - K) & 15];
-            acc[r] = FMA ? __fmaf_rn(x, tap, acc[r]) : __fadd_rn(acc[r], __fmul_rn(x, tap));
+        for (int r = 0; r != kFirOut; r += 2) {
+            float x0 = w[(r - K) & 15], x1 = w[(r + 1 - K) & 15];
+            if constexpr (FMA) acc2_fma(acc[r / 2], x0, x1, tap);
+            else acc2_add(acc[r / 2], __fmul_rn(x0, tap), __fmul_rn(x1, tap));
         }
         if constexpr (K + 1 < KEND) FirTaps<K + 1, KEND, FMA>::run(acc, w, rowp, tp);
     }
@@ -166,13 +189,19 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
         const int o0 = pass * kFirPass + warp * kFirOut;              // first output of this thread in the tile
         if (tb + (uint32_t) o0 >= head + n_new) break;                // nothing new from here on (warp-uniform)
         const float* row = xs + lane * kFirRow + kFirHalo + o0;        // sample t0
+        Acc2 acc2[kFirOut / 2];
         float acc[kFirOut], w[kFirOut];
 #pragma unroll
-        for (int r = 0; r != kFirOut; ++r) { acc[r] = 0.0f; w[r] = row[r]; }
+        for (int r = 0; r != kFirOut; ++r) w[r] = row[r];
+#pragma unroll
+        for (int r = 0; r != kFirOut / 2; ++r) acc2[r].v = 0ull;
 #pragma unroll 1
         for (int it = 0; it != kFirLoop; ++it)
-            FirTaps<0, 16, FMA>::run(acc, w, row - 16 * it, c_tab.taps + 16 * it);
-        FirTaps<0, kTapsUsed - 16 * kFirLoop, FMA>::run(acc, w, row - 16 * kFirLoop, c_tab.taps + 16 * kFirLoop);
+            FirTaps<0, 16, FMA>::run(acc2, w, row - 16 * it, c_tab.taps + 16 * it);
+        FirTaps<0, kTapsUsed - 16 * kFirLoop, FMA>::run(acc2, w, row - 16 * kFirLoop, c_tab.taps + 16 * kFirLoop);
+#pragma unroll
+        for (int r = 0; r != kFirOut / 2; ++r)
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[2 * r]), "=f"(acc[2 * r + 1]) : "l"(acc2[r].v));
 
         // 16 outputs = two 8-sample blocks; a block never straddles a 32-sample ring line.  Besides y:
         // d = x[n] - x[n-120] (the sliding DFT's `sample - oldest`, SlidingDFT.h:123-124; the 160-sample
@@ -440,6 +469,21 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, int iters, f
             for (int r = 0; r != 8; ++r)
 #pragma unroll
                 for (int i = 0; i != 16; ++i) a[i] = __fadd_rn(__fmul_rn(a[i], 0.999f), 1e-3f);
+        } else if constexpr (VARIANT == 4) {
+            // the exact-mode filter's instruction mix: two FMUL + one packed FADD2 per accumulator pair
+            float mr = out[0] * 0.f + m;
+            unsigned long long cc;
+            asm("mov.b64 %0, {%1, %1};" : "=l"(cc) : "f"(c));
+#pragma unroll
+            for (int r = 0; r != 8; ++r)
+#pragma unroll
+                for (int i = 0; i != 16; i += 2) {
+                    unsigned long long v;
+                    float p0 = __fmul_rn(a[i], mr), p1 = __fmul_rn(a[i + 1], mr);
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(p0), "f"(p1));
+                    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(v) : "l"(v), "l"(cc));
+                    asm("mov.b64 {%0, %1}, %2;" : "=f"(a[i]), "=f"(a[i + 1]) : "l"(v));
+                }
         } else {
             // register-operand FFMA (no immediates): multiplier and addend live in registers
             float mr = out[0] * 0.f + m, cr = out[1] * 0.f + c;
@@ -470,6 +514,7 @@ double run_fp32_peak(int variant, int sm_count, cudaStream_t s)
         case 0: fp32_peak_kernel<0><<<blocks, threads, 0, s>>>(buf, iters, 1.0f); break;
         case 1: fp32_peak_kernel<1><<<blocks, threads, 0, s>>>(buf, iters, 1.0f); break;
         case 2: fp32_peak_kernel<2><<<blocks, threads, 0, s>>>(buf, iters, 1.0f); break;
+        case 4: fp32_peak_kernel<4><<<blocks, threads, 0, s>>>(buf, iters, 1.0f); break;
         default: fp32_peak_kernel<3><<<blocks, threads, 0, s>>>(buf, iters, 1.0f); break;
         }
         cudaEventRecord(e1, s);

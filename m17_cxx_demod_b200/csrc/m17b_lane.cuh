@@ -52,7 +52,7 @@
 namespace m17b {
 
 #ifdef __CUDACC__
-constexpr int RS = 128;                 // shared-memory column stride == threads per CTA
+constexpr int RS = 64;                // shared-memory column stride == threads per CTA
 M17B_FN float u2f(uint32_t v) { return __uint_as_float(v); }
 M17B_FN uint32_t f2u(float v) { return __float_as_uint(v); }
 M17B_FN float mul_rn(float a, float b) { return __fmul_rn(a, b); }

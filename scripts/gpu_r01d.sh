@@ -1,0 +1,10 @@
+# usage: bash scripts/gpu_r01d.sh <tag> [ncu]  -- GPU tests, full bench line, optional steady-state ncu capture
+tag=${1:-r01d}
+mkdir -p gpurun_out
+nvidia-smi -L; nproc; free -g | head -2
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/${tag}_pytest.log
+timeout 900 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench exit $?"; tail -3 gpurun_out/${tag}_bench.err
+cat gpurun_out/${tag}_bench.json
+if [ "$2" = "ncu" ]; then
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|fir_kernel|decode_kernel' -s 170 -c 17 -o gpurun_out/${tag}_steady python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu.log 2>&1; echo "ncu exit $?"
+fi
