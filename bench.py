@@ -34,6 +34,18 @@ sys.path.insert(0, ROOT)
 ALG_FLOP_PER_SAMPLE = 300.0          # 150 multiplies + 150 adds per filtered sample
 
 
+def fir_traffic(channels, chunk, fma):
+    """DRAM bytes per fir_kernel launch from the committed ncu --set full capture (profiles/fir_dram_traffic.json),
+    or None when the capture was taken on another launch shape."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "fir_dram_traffic.json")))
+    except OSError:
+        return None
+    if fma or t["channels"] != channels or t["chunk_samples"] != chunk:
+        return None
+    return t["dram_bytes_read"] + t["dram_bytes_write"]
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -281,7 +293,7 @@ def main():
                    "generator_s": round(gen_s, 2)},
         "frames_per_s": totals["frames"] / t_max, "wall_s": t_wall, "device_s": t_dev,
         "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
-                     "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
+                     "frac": achieved / fp32_peak if fp32_peak else None, "traffic": fir_traffic(channels, T, args.fma),
                      "peak_source": "measured here: packed FFMA microkernel (m17b_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
                      "alg_flop_per_sample": ALG_FLOP_PER_SAMPLE, "avg_launch_ms": fir_ms_per_launch,
                      # the bit-identical filter must round the product and the sum separately: a multiply and an
@@ -307,6 +319,7 @@ def main():
         per = m.demod.split_by_stream(allrec, channels)
         bad = 0
         checked = 0
+        examples = []
         for s in range(channels):
             u = (lo + s) % U
             if u >= n_chk:
@@ -314,7 +327,11 @@ def main():
             checked += 1
             if not ol.records_equal(want[u], per[s]):
                 bad += 1
+                if len(examples) < 4:
+                    examples.append(f"channel {s} (waveform {u}): " + ol.describe_mismatch(want[u], per[s]))
         line["parity"] = {"channels_checked": checked, "mismatching": bad, "oracle": "ref" if ol.have_ref() else "port"}
+        if examples:
+            line["parity"]["examples"] = examples
 
     del d
     # ---- e2e: same call sequence from pinned host memory --------------------------------------

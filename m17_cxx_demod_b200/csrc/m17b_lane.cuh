@@ -31,6 +31,7 @@
 // correlator ring therefore keeps 96 samples physically (the reference's 80 plus
 // a block of look-ahead) and is addressed relative to the sample being handled.
 #pragma once
+#include <cstddef>
 
 #include "m17b_dev.cuh"
 
@@ -892,9 +893,14 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
 
     const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
     int budget = kRoundCap;
-    Chunk pf;                                               // prefetched block
-    uint32_t pf_base = 1u;                                  // never a block start: nothing prefetched yet
+    // pf always holds the block the dense pass needs next (requested one block of arithmetic earlier).
+    // There is deliberately no second, direct-load path inside the loop: ptxas gave such a path the same
+    // scoreboard as the prefetch, so the first use of the current block also waited for the prefetch
+    // that had just been issued (17 % of the kernel's stall samples, profiles/r01d).
+    Chunk pf;
+    uint32_t pf_base = dpos & ~7u;
     memset(&pf, 0, sizeof(pf));
+    if (active) load_chunk(pf, e, pf_base);
 
     while (warp_any(active)) {
         uint32_t base = 0;
@@ -925,8 +931,8 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
             if (go && jb_d < je) {
                 // this block's samples were requested one iteration ago (the lane's next 32-byte sector of
                 // its own ring line); request the next block's before the arithmetic of this one
-                Chunk c;
-                if (pf_base == base) c = pf; else load_chunk(c, e, base);
+                if (pf_base != base) ctr_add(&d.ctr->faults, 1ull);     // invariant: never happens
+                const Chunk c = pf;
                 pf_base = base + 8u;
                 load_chunk(pf, e, pf_base);
                 dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
@@ -1139,12 +1145,17 @@ M17B_FN_COLD uint32_t crc16_lsf(const uint8_t* lsf, size_t np)
 // One depunctured soft bit through the folded derandomise/deinterleave map.
 M17B_FN int soft_bit(const int16_t* llr, size_t np, int m, int stale)
 {
-    if (m == 0) return 0;
-    if (m == kMapStale) return stale;
-    int k = (m < 0 ? -m : m) - 1;
-    int pair = llr[(size_t) (k >> 1) * np];
+    // branch-free: the load is issued unconditionally (slot 0 for an erasure / the stale element), so
+    // the 16 soft bits of a block of trellis steps are 16 independent loads in flight; with early
+    // returns every call was a branch region and the loads were serialised (40 % of decode_kernel's
+    // stall samples, profiles/r01j)
+    const bool special = m == 0 || m == kMapStale;
+    const int k = special ? 0 : (m < 0 ? -m : m) - 1;
+    const int pair = llr[(size_t) (k >> 1) * np];
     int v = (k & 1) ? (int) (int8_t) (pair >> 8) : (int) (int8_t) (pair & 0xFF);
-    return m < 0 ? -v : v;
+    v = m < 0 ? -v : v;
+    v = m == 0 ? 0 : v;
+    return m == kMapStale ? stale : v;
 }
 
 // butterfly J: cost_[J][0] = +7 iff bit 2 of J, cost_[J][1] = +7 iff bit0 ^ bit1 of J
@@ -1176,20 +1187,32 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
 #pragma unroll
     for (int i = 0; i != 16; ++i) m[i] = 0x7fffffff / 2;
     m[0] = 0;
-    for (int t = 0; t != steps; ++t) {
-        int s0 = soft_bit(llr, np, map[2 * t], stale);
-        int s1 = soft_bit(llr, np, map[2 * t + 1], stale);
-        int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-        if (s0) { a0 = abs(7 - s0); a1 = abs(-7 - s0); }
-        if (s1) { b0 = abs(7 - s1); b1 = abs(-7 - s1); }
-        uint32_t h = 0;
-        butterfly<0>(m, n, h, a0, a1, b0, b1); butterfly<1>(m, n, h, a0, a1, b0, b1);
-        butterfly<2>(m, n, h, a0, a1, b0, b1); butterfly<3>(m, n, h, a0, a1, b0, b1);
-        butterfly<4>(m, n, h, a0, a1, b0, b1); butterfly<5>(m, n, h, a0, a1, b0, b1);
-        butterfly<6>(m, n, h, a0, a1, b0, b1); butterfly<7>(m, n, h, a0, a1, b0, b1);
-        hist_col[t * HS] = (uint16_t) h;
+    // Soft bits are fetched a block of 8 trellis steps ahead: 16 independent loads in flight instead of
+    // two dependent global loads in front of every add-compare-select step (the kernel is latency-bound:
+    // a handful of warps per SM, one frame per thread).
+    constexpr int kBlk = 8;
+    for (int tb = 0; tb < steps; tb += kBlk) {
+        int sbit[2 * kBlk];
 #pragma unroll
-        for (int i = 0; i != 16; ++i) m[i] = n[i];
+        for (int u = 0; u != 2 * kBlk; ++u)
+            sbit[u] = 2 * tb + u < n_in ? soft_bit(llr, np, map[2 * tb + u], stale) : 0;
+#pragma unroll
+        for (int u = 0; u != kBlk; ++u) {
+            const int t = tb + u;
+            if (t >= steps) break;
+            const int s0 = sbit[2 * u], s1 = sbit[2 * u + 1];
+            int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+            if (s0) { a0 = abs(7 - s0); a1 = abs(-7 - s0); }
+            if (s1) { b0 = abs(7 - s1); b1 = abs(-7 - s1); }
+            uint32_t h = 0;
+            butterfly<0>(m, n, h, a0, a1, b0, b1); butterfly<1>(m, n, h, a0, a1, b0, b1);
+            butterfly<2>(m, n, h, a0, a1, b0, b1); butterfly<3>(m, n, h, a0, a1, b0, b1);
+            butterfly<4>(m, n, h, a0, a1, b0, b1); butterfly<5>(m, n, h, a0, a1, b0, b1);
+            butterfly<6>(m, n, h, a0, a1, b0, b1); butterfly<7>(m, n, h, a0, a1, b0, b1);
+            hist_col[t * HS] = (uint16_t) h;
+#pragma unroll
+            for (int i = 0; i != 16; ++i) m[i] = n[i];
+        }
     }
     int min_element = 0, min_cost = m[0];
 #pragma unroll
@@ -1219,9 +1242,22 @@ M17B_FN_COLD void emit_record(const DevPtrs& d, uint32_t s, uint32_t* sb, unsign
     m17b_frame* r = d.recs + (slot & (d.rec_cap - 1));
     r->stream = s; r->seq = seq; r->sample_pos = sample_pos; r->viterbi_cost = cost;
     r->type = (uint8_t) type; r->pad[0] = r->pad[1] = r->pad[2] = 0;
+    // payload[26] + lsf[30] are contiguous in m17b_frame and 4-byte aligned: gather the 56 column bytes
+    // with independent loads first, then 14 word stores (byte stores through a uint8_t* may alias the
+    // loads, which serialised them: 25 % of decode_kernel's stall samples)
+    static_assert(offsetof(m17b_frame, payload) % 4 == 0 && offsetof(m17b_frame, lsf) == offsetof(m17b_frame, payload) + 26 &&
+                  sizeof(m17b_frame) == offsetof(m17b_frame, payload) + 56, "record layout");
     const uint8_t* b = d.dec_bytes + s;
-    for (int i = 0; i != 26; ++i) r->payload[i] = b[(size_t) i * d.np];
-    for (int i = 0; i != 30; ++i) r->lsf[i] = b[(size_t) (26 + i) * d.np];
+    uint32_t wv[14];
+#pragma unroll
+    for (int i = 0; i != 14; ++i) {
+        uint32_t b0 = b[(size_t) (4 * i) * d.np], b1 = b[(size_t) (4 * i + 1) * d.np];
+        uint32_t b2 = b[(size_t) (4 * i + 2) * d.np], b3 = b[(size_t) (4 * i + 3) * d.np];
+        wv[i] = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+    }
+    uint32_t* dst = reinterpret_cast<uint32_t*>(r->payload);
+#pragma unroll
+    for (int i = 0; i != 14; ++i) dst[i] = wv[i];
 }
 
 // unpack_lich, M17FrameDecoder.h:181-215, with Golay24::decode (Golay24.h:203-222).

@@ -19,7 +19,9 @@
 #include "m17_oracle.h"
 
 #include <cstdlib>
+#include <cerrno>
 #include <cstring>
+#include <deque>
 #include <new>
 #include <cstdio>
 #include <vector>
@@ -143,9 +145,20 @@ int m17ref_demod_batch(const int16_t* samples, size_t n_streams, size_t n_sample
     auto* scnt = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(shm) + rec_bytes);
     auto* strc = trace ? reinterpret_cast<m17o_trace*>(reinterpret_cast<char*>(shm) + rec_bytes + cnt_bytes) : nullptr;
 
-    int live = 0, status = 0, rc = 0;
+    // Children are reaped by pid, oldest first: a plain wait() would also collect unrelated children of
+    // the calling process (bench.py's nvidia-smi sampler), miscount the live oracle processes and
+    // return while one of them is still writing its records.
+    std::deque<pid_t> pids;
+    int status = 0, rc = 0;
+    auto reap_oldest = [&]() {
+        pid_t p = pids.front();
+        pids.pop_front();
+        pid_t r;
+        do { r = waitpid(p, &status, 0); } while (r < 0 && errno == EINTR);
+        if (r != p || !WIFEXITED(status) || WEXITSTATUS(status) != 0) rc = -2;
+    };
     for (size_t s = 0; s != n_streams; ++s) {
-        while (live >= jobs) { if (wait(&status) > 0) { --live; if (status) rc = -2; } }
+        while ((int) pids.size() >= jobs) reap_oldest();
         pid_t pid = fork();
         if (pid < 0) { rc = -3; break; }
         if (pid == 0) {
@@ -154,9 +167,9 @@ int m17ref_demod_batch(const int16_t* samples, size_t n_streams, size_t n_sample
                                         strc ? strc + s * n_samples : nullptr);
             _exit(0);
         }
-        ++live;
+        pids.push_back(pid);
     }
-    while (live > 0) { if (wait(&status) > 0) { --live; if (status) rc = -2; } }
+    while (!pids.empty()) reap_oldest();
     std::memcpy(rec, srec, rec_bytes);
     std::memcpy(counts, scnt, cnt_bytes);
     if (trace) std::memcpy(trace, strc, trc_bytes);
