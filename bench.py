@@ -278,9 +278,9 @@ def main():
     fir_ms_per_launch = prof.fir_ms / max(1, prof.fir_launches)
     fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
-    kernel_ms = {"fir": prof.fir_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "aux": prof.aux_ms}
+    kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "aux": prof.aux_ms}
     ksum = sum(kernel_ms.values()) or 1.0
-    launches = int(prof.fir_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches)
+    launches = int(prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches)
 
     line = {
         "metric": "baseband_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -386,7 +386,7 @@ def main():
                        "h2d_bytes_per_step": channels * T * 2, "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
                        "frames_per_s": world * fr / te, "pipeline_depth": DEPTH,
                        "ms_between_drains": [round(1e3 * (b - a), 2) for a, b in zip([t0] + marks[:-1], marks)],
-                       "kernel_ms_per_step": {"fir": prof_e.fir_ms / Ke, "scan": prof_e.scan_ms / Ke,
+                       "kernel_ms_per_step": {"fir": prof_e.fir_ms / Ke, "dcd": prof_e.dcd_ms / Ke, "scan": prof_e.scan_ms / Ke,
                                               "decode": prof_e.decode_ms / Ke, "h2d": prof_e.h2d_ms / Ke},
                        "h2d_gbs": (prof_e.h2d_bytes / (prof_e.h2d_ms * 1e-3) / 1e9) if prof_e.h2d_ms else None,
                        "timing": "host clock around Ke submit+drain pairs incl. pipeline fill and final drain"}

@@ -129,6 +129,7 @@ typedef struct m17b_profile {
     double   aux_ms;     uint64_t aux_launches;                              /* history tail upkeep              */
     double   h2d_ms;     uint64_t h2d_bytes;
     double   d2h_ms;     uint64_t d2h_bytes;
+    double   dcd_ms;     uint64_t dcd_launches;                              /* carrier-detect pre-pass          */
 } m17b_profile;
 
 uint32_t    m17b_version(void);

@@ -57,7 +57,7 @@ struct m17b_ctx {
 
 namespace {
 
-enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H };
+enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H, CAT_DCD };
 
 int fail(m17b_ctx* c, cudaError_t e, const char* what)
 {
@@ -96,6 +96,7 @@ void ev_collect(m17b_ctx* c)
             case CAT_DECODE: c->prof.decode_ms += ms; break;
             case CAT_AUX: c->prof.aux_ms += ms; break;
             case CAT_H2D: c->prof.h2d_ms += ms; break;
+            case CAT_DCD: c->prof.dcd_ms += ms; break;
             default: c->prof.d2h_ms += ms; break;
             }
         }
@@ -109,7 +110,7 @@ int run_round(m17b_ctx* c)
     EvPair p{};
     CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 7 * sizeof(unsigned int), c->compute));      // lagging, fix_count, dec_count[5]
     ev_begin(c, c->compute, CAT_SCAN, p);
-    launch_scan(c->d, c->head, c->compute);
+    launch_scan(c->d, c->head, c->head64, c->compute);
     ev_end(c, c->compute, p);
     c->prof.scan_launches += 1;
     ev_begin(c, c->compute, CAT_DECODE, p);
@@ -178,7 +179,7 @@ void free_all(m17b_ctx* c)
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
     for (auto& e : c->done) if (e) cudaEventDestroy(e);
     if (c->snap) cudaFreeHost(c->snap);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -264,6 +265,11 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.ring_x, ring_bytes / 2));
         CK(cudaMalloc(&d.corr_ring, 96 * np * sizeof(float)));
         CK(cudaMalloc(&d.lim_save, 8 * np * sizeof(float)));
+        // a scan lane may lag the head by the ring span; its window starts up to 960 samples earlier, and the
+        // first window's entry must survive 1920 samples longer
+        d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
+        CK(cudaMalloc(&d.seg_ring, (size_t) d.n_seg * 4 * np * sizeof(float)));
+        CK(cudaMemsetAsync(d.seg_ring, 0, (size_t) d.n_seg * 4 * np * sizeof(float), c->compute));
         CK(cudaMalloc(&d.fix_list, np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.dec_list, 5 * np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
@@ -385,6 +391,11 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
         launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], c->compute);
         ev_end(c, c->compute, p);
     }
+    // carrier-detect pre-pass over the new samples (reads ring_d written by the filter)
+    ev_begin(c, c->compute, CAT_DCD, p);
+    launch_dcd(c->d, c->head, (uint32_t) n, c->head64, c->compute);
+    ev_end(c, c->compute, p);
+    c->prof.dcd_launches += 1;
     CK(cudaGetLastError());
     c->cur_tail ^= 1;
     c->prof.fir_launches += 1;

@@ -20,6 +20,8 @@
 //       128 B line per field per warp)
 //   correlator ring               : float [96][Np]    (Correlator::buffer_ + one block of look-ahead)
 //   limit look-ahead              : float [8][Np]     (limit_ of samples the dense pass ran ahead by)
+//   carrier-detect window sums    : float [n_seg][4][Np]  (dcd_kernel: energy sums of both sliding-DFT bins
+//                                   384 and 960 samples after every 192-aligned window start)
 //   sync-word peak samples        : float [30][Np]    (SyncWord::samples_ x3)
 //   FIR history snapshot          : float [149][Np]   (taken when DCD gates the filter)
 //   soft-bit frame                : int16 [184][Np]   (M17Framer buffer, 2 LLRs per symbol)
@@ -41,6 +43,8 @@ constexpr int kLine = 32;             // samples per ring line (128 bytes of flo
 constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:149: 48000/400)
 constexpr int kRoundCap = 2048;       // samples a stream may advance per scan launch
 constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
+constexpr int kSeg = 192;             // gcd of the carrier-detect cadences 384 / 960 and of the 1920-sample start-up
+constexpr int kFirstUpdate = 1920 + 384;   // position of a stream's first carrier-detect update (M17Demodulator.h:659-689)
 
 enum Field : int {
     F_POS = 0,
@@ -62,7 +66,9 @@ enum Field : int {
     F_RP,           // next physical slot of the 96-entry correlator ring
     F_GAPR,         // position at which the matched filter last resumed after a carrier-detect gap
     F_GAPDONE,      // outputs after F_GAPR already corrected by fixup_kernel (0..149)
-    NFIELDS
+    F_ACC1,         // dcd_kernel: five rolling carrier-detect energy sums of bin 0 (window phases), F_ACC1 + i
+    F_ACC2 = F_ACC1 + 5,   // ... of bin 1
+    NFIELDS = F_ACC2 + 5
 };
 
 // F_FLAGS bit layout
@@ -103,6 +109,7 @@ struct DevPtrs {
     int16_t* ring_x;              // [RL][Np][32]
     float* corr_ring;             // [96][Np]
     float* lim_save;              // [8][Np]
+    float* seg_ring;              // [n_seg][4][Np] carrier-detect energy sums per window start (see dcd_lane)
     uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
     uint32_t* dec_list;           // [5][Np] streams with a completed frame, by decode kind (0..3 = Viterbi map, 4 = LICH / none)
     float* sw_samples;            // [30][Np]
@@ -114,6 +121,7 @@ struct DevPtrs {
     uint32_t n_streams;
     uint32_t np;                  // padded stream count (multiple of 128)
     uint32_t ring_lines;          // RL, power of two
+    uint32_t n_seg;               // entries of seg_ring, power of two, n_seg * 192 > ring span + 960
     uint32_t rec_cap;             // power of two
     uint32_t rec_read;            // cursor up to which the host has taken the records (at launch time)
 };
@@ -150,7 +158,8 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
                 uint32_t head, bool fma, bool invert, cudaStream_t s);
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
-void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s);
+void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);

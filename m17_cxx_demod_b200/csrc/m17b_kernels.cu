@@ -296,8 +296,23 @@ namespace m17b {
 constexpr int kScanThreads = RS;
 constexpr size_t kScanSmem = sizeof(float) * (kRing + 8) * kScanThreads + sizeof(LlrTable);
 
+// Carrier-detect pre-pass (dcd_lane) over the new samples of a submit, all lanes
+// at the same position, two lanes (one per DFT bin) per stream.  Bound: FP32 issue; reads ring_d once (4 B/sample).
+__global__ void __launch_bounds__(128)
+dcd_kernel(DevPtrs d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;      // lane pair = the two bins of one stream
+    if ((t >> 1) >= d.n_streams) return;
+    dcd_lane(d, t >> 1, (int) (t & 1u), head_old, n_new, head64_old);
+}
+
+void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s)
+{
+    dcd_kernel<<<(2 * d.n_streams + 127) / 128, 128, 0, s>>>(d, head_old, n_new, head64_old);
+}
+
 __global__ void __launch_bounds__(kScanThreads)
-scan_kernel(DevPtrs d, uint32_t head)
+scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
 {
     extern __shared__ float smem[];
     float* ring_s = smem;                                  // [96][128] correlator rings
@@ -328,12 +343,12 @@ scan_kernel(DevPtrs d, uint32_t head)
     e.np = d.np;
     e.lmask = d.ring_lines - 1;
     e.s = s;
-    scan_lane(d, e, head, s < d.n_streams);
+    scan_lane(d, e, head, head64, s < d.n_streams);
 }
 
-void launch_scan(const DevPtrs& d, uint32_t head, cudaStream_t s)
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
 {
-    scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head);
+    scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head, head64);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to

@@ -381,7 +381,7 @@ M17B_FN uint32_t llr4(const LlrTable& tab, float sample)
 
 // Per-lane working set of the scan.
 struct Scan {
-    float re0, im0, re1, im1, l1, l2, level;   // NSlidingDFT bins, DCD accumulators, DCD level
+    float level;                               // DCD level (the sliding DFT and its energy sums live in dcd_lane)
     float iir0, iir1, limit;                   // limit biquad history / output
     float idev, offset, evm;
     float ck_est, ck_sest;
@@ -431,10 +431,10 @@ M17B_FN int do_sync_step(Scan& z, const LaneIo& e, int k, uint32_t word, float m
 }
 
 // DataCarrierDetect.h:63-69 (ltrigger 0.1, htrigger 4.0)
-M17B_FN void dcd_update(Scan& z)
+// l1 / l2 = the energy sums of the two sliding-DFT bins over the window that ends here (dcd_sums)
+M17B_FN void dcd_update(Scan& z, float l1, float l2)
 {
-    z.level = (float) ((double) z.level * 0.8 + 0.2 * (double) (z.l1 / z.l2));
-    z.l1 = 0.f; z.l2 = 0.f;
+    z.level = (float) ((double) z.level * 0.8 + 0.2 * (double) (l1 / l2));
     z.dcd_trig = z.dcd_trig ? z.level > 0.1f : z.level > 4.0f;
 }
 
@@ -786,35 +786,25 @@ M17B_FN void event_step(Scan& z, const LaneIo& e)
     }
 }
 
-struct Chunk { float y[8], d[8]; };      // one block of ring_y / ring_d
+struct Chunk { float y[8]; };            // one block of ring_y
 
 M17B_FN void load_chunk(Chunk& c, const LaneIo& e, uint32_t base)
 {
     const size_t o = ring_off(base, e.lmask, e.np, e.s);
     const float4* py = reinterpret_cast<const float4*>(e.ring_y + o);
-    const float4* pd = reinterpret_cast<const float4*>(e.ring_d + o);
-    float4 a0 = py[0], a1 = py[1], b0 = pd[0], b1 = pd[1];
+    float4 a0 = py[0], a1 = py[1];
     c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
-    c.d[0] = b0.x; c.d[1] = b0.y; c.d[2] = b0.z; c.d[3] = b0.w; c.d[4] = b1.x; c.d[5] = b1.y; c.d[6] = b1.z; c.d[7] = b1.w;
 }
 
-// Dense pass over samples [jb, je) of the block starting at absolute position `base`.
-M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base,
-                         float c0r, float c0i, float c1r, float c1i)
+// Dense pass over samples [jb, je) of the block starting at absolute position `base`: the per-sample
+// recurrences of the clocked path (the carrier detect's sliding DFT, which runs on every sample whatever
+// the state, is dcd_lane's).
+M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base)
 {
+    if (!clocked) return;               // :675-689: the filter and the correlator are not clocked while !dcd_
 #pragma unroll
     for (int j = 0; j != 8; ++j) {
         if (j < jb || j >= je) continue;
-        {   // dcd(input): SlidingDFT.h:118-132, DataCarrierDetect.h:53-58
-            float delta = c.d[j];           // sample - oldest, formed by fir_kernel
-            float a = z.re0 + delta, b = z.im0;
-            z.re0 = a * c0r - b * c0i; z.im0 = a * c0i + b * c0r;
-            a = z.re1 + delta; b = z.im1;
-            z.re1 = a * c1r - b * c1i; z.im1 = a * c1i + b * c1r;
-            z.l1 += z.re0 * z.re0 + z.im0 * z.im0;
-            z.l2 += z.re1 * z.re1 + z.im1 * z.im1;
-        }
-        if (!clocked) continue;         // :675-689: the filter and the correlator are not clocked while !dcd_
         // the matched filter has run speculatively on every sample; the 149 outputs after a
         // carrier-detect gap have been replaced by fixup_kernel before the lane gets here
         float filtered = c.y[j];
@@ -838,12 +828,117 @@ M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int j
     }
 }
 
+// ---------------------------------------------------------------------------
+// Carrier-detect pre-pass.  DataCarrierDetect::operator() (DataCarrierDetect.h:53-58) clocks the two-bin
+// sliding DFT (SlidingDFT.h:118-132) on EVERY input sample, whatever the demodulator state, and sums
+// the bin energies until the next update(), every 384 samples while !dcd_ and every 960 while dcd_
+// (M17Demodulator.h:675-689,742-752), after a first window of 1920 + 384 samples.  Every update lands
+// on a multiple of 192 samples from the start of the stream, and a window's sums depend only on where
+// it starts and how long it is.  dcd_lane runs the recurrence once per submit for all streams in
+// lock-step (every lane at the same position: no divergence, none of the scan's register pressure)
+// and keeps five staggered sums per bin, one per 192-sample phase of a 960-sample cycle; each sum is
+// recorded 384 and 960 samples after its start.  The scan looks the pair up at its update points
+// (dcd_sums): the same sequence of float additions as the reference, so the level is bit-identical.
+// seg_ring entry q (window starting at sample 192 q): {l1@384, l2@384, l1@960, l2@960}; the first
+// window [0, 2304) is stored in entry 0 in place of its unused @384 pair.
+// ---------------------------------------------------------------------------
+// One lane = one DFT bin of one stream (bin 0 or 1: the two bins and their sums are independent
+// recurrences, so a stream is split over two neighbouring lanes that read the same samples).
+M17B_FN void dcd_lane(const DevPtrs& d, uint32_t s, int bin, uint32_t head_old, uint32_t n_new, unsigned long long head64_old)
+{
+    uint32_t* sb = d.st + st_index(s, 0);
+    const int f_re = bin ? F_RE1 : F_RE0, f_im = bin ? F_IM1 : F_IM0, f_first = bin ? F_L2 : F_L1, f_acc = bin ? F_ACC2 : F_ACC1;
+    float re = u2f(sb[f_re * 32]), im = u2f(sb[f_im * 32]);
+    float first = u2f(sb[f_first * 32]);                          // first window [0, 2304)
+    float acc[5];
+#pragma unroll
+    for (int i = 0; i != 5; ++i) acc[i] = u2f(sb[(f_acc + i) * 32]);
+    const float cr = M17B_TAB.sdft[2 * bin], ci = M17B_TAB.sdft[2 * bin + 1];
+    uint32_t seg = (uint32_t) (head64_old / kSeg);       // ordinal of the segment the next sample is in
+    uint32_t age = (uint32_t) (head64_old % kSeg);
+    uint32_t m5 = seg % 5u;
+    const uint32_t lmask = d.ring_lines - 1, smask = d.n_seg - 1;
+    const size_t np = d.np;
+    float* const ring = d.seg_ring + (size_t) bin * np + s;       // slot k = bin (@384) / 2 + bin (@960)
+    // per sample: SlidingDFT.h:118-132 for this bin, its energy (DataCarrierDetect.h:53-58), the sums
+#define M17B_DCD_STEP(x_)                                                        \
+    do {                                                                         \
+        const float a_ = re + (x_), b_ = im;   /* x_ = sample - oldest, formed by fir_kernel */ \
+        re = a_ * cr - b_ * ci; im = a_ * ci + b_ * cr;                          \
+        const float e_ = re * re + im * im;                                      \
+        if (in_first) first += e_;                                               \
+        _Pragma("unroll") for (int i_ = 0; i_ != 5; ++i_) acc[i_] += e_;         \
+    } while (0)
+    // a 192-sample segment ends: record the sums that are 384 / 960 samples old, restart the latter
+#define M17B_DCD_BOUNDARY()                                                      \
+    do {                                                                         \
+        age = 0;                                                                 \
+        ++seg;                                  /* the segment that starts with the next sample */ \
+        m5 = m5 == 4u ? 0u : m5 + 1u;                                            \
+        if (seg == (uint32_t) (kFirstUpdate / kSeg)) { ring[0] = first; in_first = false; } \
+        _Pragma("unroll") for (int i_ = 0; i_ != 5; ++i_) {                      \
+            const uint32_t ph_ = m5 >= (uint32_t) i_ ? m5 - (uint32_t) i_ : m5 + 5u - (uint32_t) i_; \
+            if (ph_ == 2u) ring[(size_t) ((seg - 2u) & smask) * 4 * np] = acc[i_]; \
+            if (ph_ == 0u) { ring[((size_t) ((seg - 5u) & smask) * 4 + 2) * np] = acc[i_]; acc[i_] = 0.f; } \
+        }                                                                        \
+    } while (0)
+    bool in_first = seg < (uint32_t) (kFirstUpdate / kSeg);
+    const uint32_t n_blk = ((head_old & 7u) + n_new + 7u) >> 3;
+    uint32_t base = head_old & ~7u;
+    const float4* pd = reinterpret_cast<const float4*>(d.ring_d + ring_off(base, lmask, d.np, s));
+    float4 q0 = pd[0], q1 = pd[1];
+    for (uint32_t b = 0; b != n_blk; ++b, base += 8u) {
+        const float dl[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        // next block requested before this one's arithmetic (one block past the end is inside the ring)
+        pd = reinterpret_cast<const float4*>(d.ring_d + ring_off(base + 8u, lmask, d.np, s));
+        q0 = pd[0]; q1 = pd[1];
+        const uint32_t rel = base - head_old;               // wraps for the partial first block
+        if (rel < n_new && n_new - rel >= 8u) {
+            // whole block inside the submit; blocks are 8-aligned in stream time, so a segment can only end
+            // with the block (192 = 24 blocks)
+#pragma unroll
+            for (int j = 0; j != 8; ++j) M17B_DCD_STEP(dl[j]);
+            age += 8u;
+            if (age == (uint32_t) kSeg) M17B_DCD_BOUNDARY();
+        } else {
+#pragma unroll
+            for (int j = 0; j != 8; ++j) {
+                if ((uint32_t) (rel + (uint32_t) j) >= n_new) continue;
+                M17B_DCD_STEP(dl[j]);
+                if (++age == (uint32_t) kSeg) M17B_DCD_BOUNDARY();
+            }
+        }
+    }
+#undef M17B_DCD_STEP
+#undef M17B_DCD_BOUNDARY
+    sb[f_re * 32] = f2u(re); sb[f_im * 32] = f2u(im);
+    sb[f_first * 32] = f2u(first);
+#pragma unroll
+    for (int i = 0; i != 5; ++i) sb[(f_acc + i) * 32] = f2u(acc[i]);
+}
+
+// Energy sums of the carrier-detect window of w samples that ends at the scan position `pos`.
+M17B_FN void dcd_sums(const DevPtrs& d, const LaneIo& e, uint32_t pos, uint32_t head, unsigned long long head64, int w,
+                      float& l1, float& l2)
+{
+    const unsigned long long u = head64 - (unsigned long long) (head - pos);
+    uint32_t q = 0;
+    int k = 0;
+    if (u != (unsigned long long) kFirstUpdate) {
+        q = (uint32_t) ((u - (unsigned long long) w) / kSeg);
+        k = w == 384 ? 0 : 2;
+    }
+    const float* p = d.seg_ring + ((size_t) (q & (d.n_seg - 1)) * 4 + (size_t) k) * d.np + e.s;
+    l1 = p[0];
+    l2 = p[d.np];
+}
+
 // Walk this lane from its position towards `head`; on return the lane is at head, stopped on
 // a completed frame (FL_PENDING, decode_kernel's turn), waiting for a filter fix-up (FL_FIXUP)
 // or out of budget.  Called by all 32 lanes of a warp together (`valid` = the lane has a stream):
 // the block loop is warp-synchronous so that the lanes can evaluate the sync-word correlations of
 // a searching lane's block between them (corr_bit).
-M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool valid)
+M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigned long long head64, bool valid)
 {
     uint32_t* sb = e.sb;
     uint32_t pos = valid ? sb[F_POS * 32] : head;
@@ -865,9 +960,6 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
     dpos = sb[F_DPOS * 32];
     gap_r = sb[F_GAPR * 32];
     gap_done = (int) sb[F_GAPDONE * 32];
-    z.re0 = u2f(sb[F_RE0 * 32]); z.im0 = u2f(sb[F_IM0 * 32]);
-    z.re1 = u2f(sb[F_RE1 * 32]); z.im1 = u2f(sb[F_IM1 * 32]);
-    z.l1 = u2f(sb[F_L1 * 32]); z.l2 = u2f(sb[F_L2 * 32]);
     z.level = u2f(sb[F_LEVEL * 32]);
     z.iir0 = u2f(sb[F_IIR0 * 32]); z.iir1 = u2f(sb[F_IIR1 * 32]);
     z.limit = u2f(sb[F_LIMIT * 32]);
@@ -891,7 +983,6 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
         for (int j = (int) (pos & 7); j != 8; ++j) e.lim[j * RS] = d.lim_save[(size_t) j * d.np + e.s];
     }
 
-    const float c0r = M17B_TAB.sdft[0], c0i = M17B_TAB.sdft[1], c1r = M17B_TAB.sdft[2], c1i = M17B_TAB.sdft[3];
     int budget = kRoundCap;
     // pf always holds the block the dense pass needs next (requested one block of arithmetic earlier).
     // There is deliberately no second, direct-load path inside the loop: ptxas gave such a path the same
@@ -935,7 +1026,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
                 const Chunk c = pf;
                 pf_base = base + 8u;
                 load_chunk(pf, e, pf_base);
-                dense_block(z, e, c, jb_d, je, clocked, base, c0r, c0i, c1r, c1i);
+                dense_block(z, e, c, jb_d, je, clocked, base);
                 const int n = je - jb_d;
                 if (initializing) z.init -= n;              // count_ stays 0 while initializing
                 else z.count += n;
@@ -1008,15 +1099,19 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
                     }
                 } else if (!z.dcd) {
                     if (z.count == 384) {                   // :675-689
+                        float l1, l2;
+                        dcd_sums(d, e, pos, head, head64, 384, l1, l2);
                         update_dcd(z, e);
-                        dcd_update(z);
+                        dcd_update(z, l1, l2);
                         z.count = 0;
                         if (z.dcd) { gap_r = pos; gap_done = 0; }   // the filter resumes with the next sample
                     }
                 } else if (z.count == 960) {                // :742-752
+                    float l1, l2;
+                    dcd_sums(d, e, pos, head, head64, 960, l1, l2);
                     update_dcd(z, e);
                     z.count = 0;
-                    dcd_update(z);
+                    dcd_update(z, l1, l2);
                     if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, z.gap_k);
                 }
             }
@@ -1028,9 +1123,6 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, bool va
     // write back
     sb[F_POS * 32] = pos;
     sb[F_DPOS * 32] = dpos;
-    sb[F_RE0 * 32] = f2u(z.re0); sb[F_IM0 * 32] = f2u(z.im0);
-    sb[F_RE1 * 32] = f2u(z.re1); sb[F_IM1 * 32] = f2u(z.im1);
-    sb[F_L1 * 32] = f2u(z.l1); sb[F_L2 * 32] = f2u(z.l2);
     sb[F_LEVEL * 32] = f2u(z.level);
     sb[F_IIR0 * 32] = f2u(z.iir0); sb[F_IIR1 * 32] = f2u(z.iir1);
     sb[F_LIMIT * 32] = f2u(z.limit);

@@ -47,7 +47,8 @@ class Profile(ctypes.Structure):
                 ("decode_ms", ctypes.c_double), ("decode_launches", ctypes.c_uint64), ("decode_frames", ctypes.c_uint64),
                 ("aux_ms", ctypes.c_double), ("aux_launches", ctypes.c_uint64),
                 ("h2d_ms", ctypes.c_double), ("h2d_bytes", ctypes.c_uint64),
-                ("d2h_ms", ctypes.c_double), ("d2h_bytes", ctypes.c_uint64)]
+                ("d2h_ms", ctypes.c_double), ("d2h_bytes", ctypes.c_uint64),
+                ("dcd_ms", ctypes.c_double), ("dcd_launches", ctypes.c_uint64)]
 
 
 _lib = None

@@ -30,7 +30,7 @@ uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p
 struct Emu {
     DevPtrs d{};
     std::vector<uint32_t> st;
-    std::vector<float> ring_y, ring_d, corr_ring, lim_save, sw_samples, fir_snap;
+    std::vector<float> ring_y, ring_d, corr_ring, lim_save, sw_samples, fir_snap, seg_ring;
     std::vector<int16_t> llr, ring_x;
     std::vector<uint32_t> fix_list, dec_list;
     std::vector<uint8_t> dec_bytes;
@@ -62,6 +62,8 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.ring_x.assign((size_t) d.ring_lines * np * kLine, 0);
     m.corr_ring.assign(kRing * np, 0.f);
     m.lim_save.assign(8 * np, 0.f);
+    d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
+    m.seg_ring.assign((size_t) d.n_seg * 4 * np, 0.f);
     m.fix_list.assign(np, 0);
     m.dec_list.assign(5 * np, 0);
     m.sw_samples.assign(30 * np, 0.f);
@@ -70,7 +72,7 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.dec_bytes.assign(56 * np, 0);
     m.recs.resize(d.rec_cap);
     d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
-    d.lim_save = m.lim_save.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
+    d.lim_save = m.lim_save.data(); d.seg_ring = m.seg_ring.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
     for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
 }
@@ -90,7 +92,7 @@ void round(Emu& m)
         e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
         e.ring_y = d.ring_y; e.ring_d = d.ring_d; e.ring_x = d.ring_x;
         e.np = d.np; e.lmask = d.ring_lines - 1; e.s = s;
-        scan_lane(d, e, m.head, true);
+        scan_lane(d, e, m.head, m.head64, true);
     }
     uint16_t hist[244];
     for (int k = 0; k != 5; ++k)
@@ -142,6 +144,7 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
                 m.ring_d[o] = x[s * n + t] - (t >= (size_t) kDftN ? x[s * n + t - kDftN] : 0.f);
                 m.ring_x[o] = (int16_t) v;
             }
+        for (uint32_t s = 0; s != d.n_streams; ++s) { dcd_lane(d, s, 0, m.head, c, m.head64); dcd_lane(d, s, 1, m.head, c, m.head64); }
         m.head += c; m.head64 += c; off += c;
         int rounds = (int) (c / kMinFrameSpacing) + 2;
         for (int r = 0; r != rounds; ++r) round(m);
