@@ -218,7 +218,7 @@ def main():
     assert big.is_contiguous()
     torch.cuda.synchronize()
 
-    flags = m.PROFILE | (m.FIR_FMA if args.fma else 0)
+    flags = m.PROFILE | m.STREAMING | (m.FIR_FMA if args.fma else 0)
     rec_cap = min(channels * 2 * (T // 1600 + 2) * 3, 2**31 - 1)          # two steps in flight
     d = m.Demodulator(channels, T, flags=flags, device=local, frame_capacity=rec_cap)
     fp32_peak = d.measure_fp32_peak(1)
@@ -275,7 +275,17 @@ def main():
     totals = gather_counters({"frames": n_frames, "samples": channels * K * T}, world, dev if world > 1 else None)
 
     value = totals["samples"] / t_max / 1e6
-    fir_ms_per_launch = prof.fir_ms / max(1, prof.fir_launches)
+    # Roofline probe.  In M17B_STREAMING mode the catch-up rounds of step k share the SMs with the matched filter
+    # of step k+1, so the filter's in-step launch time includes that time-sharing.  Three more submits, each
+    # followed by m17b_sync, time the same launch (same shapes, same resident data) with nothing else running.
+    fir_in_step_ms = prof.fir_ms / max(1, prof.fir_launches)
+    d.profile(reset=True)
+    for k in range(3):
+        d.submit_device(big.data_ptr() + 2 * k * T, T, total)
+        d.sync()
+    d.drain()
+    prof_alone = d.profile()
+    fir_ms_per_launch = prof_alone.fir_ms / max(1, prof_alone.fir_launches)
     fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
     kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "aux": prof.aux_ms}
@@ -290,12 +300,17 @@ def main():
                    "filter": "fma" if args.fma else "exact (reference mul-then-add order, bit-identical)",
                    "l2": f"inputs larger than L2 ({channels * T * 2 / 1e6:.0f} MB of int16 per step, never re-read)",
                    "drain": "records of step k read back (m17b_drain_upto) while step k+1 runs; all inside the timed region",
+                   "mode": "M17B_STREAMING (streams walk whole frames; every frame ending in a step is delivered with that step)",
                    "generator_s": round(gen_s, 2)},
         "frames_per_s": totals["frames"] / t_max, "wall_s": t_wall, "device_s": t_dev,
         "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": achieved / fp32_peak if fp32_peak else None, "traffic": fir_traffic(channels, T, args.fma),
                      "peak_source": "measured here: packed FFMA microkernel (m17b_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
                      "alg_flop_per_sample": ALG_FLOP_PER_SAMPLE, "avg_launch_ms": fir_ms_per_launch,
+                     "timing": "CUDA events around 3 fir_kernel launches run alone right after the timed region (same shapes and data)",
+                     "in_step": {"avg_launch_ms": fir_in_step_ms,
+                                 "frac": (achieved * fir_ms_per_launch / fir_in_step_ms / fp32_peak) if fp32_peak and fir_in_step_ms else None,
+                                 "note": "inside the timed steps the launch shares the SMs with the previous step's catch-up scan rounds (side stream)"},
                      # the bit-identical filter must round the product and the sum separately: a multiply and an
                      # add per tap instead of one FFMA, i.e. at most half the FFMA-counted peak.  Measured here
                      # with the same instruction mix (FMUL+FADD, and 2 FMUL + 1 packed FADD2 as the kernel issues).
@@ -341,7 +356,7 @@ def main():
         if (Ke + NW) * T > total:
             Ke = total // T - NW
         DEPTH = 2                                              # submits enqueued ahead of the record read-back
-        de = m.Demodulator(channels, T, flags=m.PROFILE, device=local,
+        de = m.Demodulator(channels, T, flags=m.PROFILE | m.STREAMING, device=local,
                            frame_capacity=min(channels * (DEPTH + 2) * (T // 1600 + 2) * 3, 2**31 - 1))
         bufs = [m.demod.PinnedBuffer((channels, T)) for _ in range(Ke + NW)]
         idx_h = (np.arange(lo, hi) % U)

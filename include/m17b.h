@@ -54,6 +54,11 @@ extern "C" {
                                   (FirFilter.h:36-40), bit-identical filter outputs.            */
 #define M17B_INVERT      0x2u  /* `sample *= -1` before scaling (apps/m17-demod.cpp:488, -i)   */
 #define M17B_PROFILE     0x4u  /* record CUDA events around every kernel (m17b_get_profile)    */
+#define M17B_STREAMING   0x8u  /* back-to-back submits (m17b_ticket / m17b_drain_upto): between submits a
+                                * stream may trail the newest sample by less than one frame, so that it
+                                * always walks whole frames.  Every frame that ends inside a submit is still
+                                * delivered with that submit; m17b_sync / m17b_drain bring all streams up to
+                                * the newest sample first (their diagnostics then match the reference's).  */
 
 /* m17b_submit location */
 #define M17B_HOST    0         /* samples points to host memory (pinned for full overlap)      */

@@ -5,8 +5,8 @@ package is a thin ctypes binding used by the tests and by ``bench.py``.  There i
 no CPU fallback: without the built library or without a CUDA device every entry
 point raises.
 """
-from .demod import (Demodulator, FRAME_DTYPE, FRAME_TYPE_NAMES, PAYLOAD_LEN, FIR_FMA, INVERT, PROFILE,
+from .demod import (Demodulator, FRAME_DTYPE, FRAME_TYPE_NAMES, PAYLOAD_LEN, FIR_FMA, INVERT, PROFILE, STREAMING,
                     M17BError, library_path, load_library, device_count)
 
-__all__ = ["Demodulator", "FRAME_DTYPE", "FRAME_TYPE_NAMES", "PAYLOAD_LEN", "FIR_FMA", "INVERT", "PROFILE",
+__all__ = ["Demodulator", "FRAME_DTYPE", "FRAME_TYPE_NAMES", "PAYLOAD_LEN", "FIR_FMA", "INVERT", "PROFILE", "STREAMING",
            "M17BError", "library_path", "load_library", "device_count"]

@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -33,6 +34,11 @@ struct m17b_ctx {
     cudaEvent_t stage_free[2] = {nullptr, nullptr}, stage_ready[2] = {nullptr, nullptr};
     int cur_stage = 0;
     cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;   // kernels; sample H2D; record D2H
+    // M17B_STREAMING: the catch-up rounds of a submit (after its whole-frame rounds) run on `side`, under the
+    // matched filter of the next submit; ev_side marks their end
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_main = nullptr, ev_side = nullptr;
+    bool side_pending = false;
     uint32_t head = 0;
     unsigned long long head64 = 0;
     int sm_count = 0;
@@ -105,28 +111,40 @@ void ev_collect(m17b_ctx* c)
     c->ev_live.clear();
 }
 
-int run_round(m17b_ctx* c)
+int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard = 0)
 {
     EvPair p{};
-    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 7 * sizeof(unsigned int), c->compute));      // lagging, fix_count, dec_count[5]
-    ev_begin(c, c->compute, CAT_SCAN, p);
-    launch_scan(c->d, c->head, c->head64, c->compute);
-    ev_end(c, c->compute, p);
+    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 8 * sizeof(unsigned int), st));      // lagging, fix_count, dec_count[5], deferred
+    ev_begin(c, st, CAT_SCAN, p);
+    launch_scan(c->d, c->head, c->head64, defer, guard, st);
+    ev_end(c, st, p);
     c->prof.scan_launches += 1;
-    ev_begin(c, c->compute, CAT_DECODE, p);
-    launch_decode(c->d, c->head, c->head64, c->compute);
-    ev_end(c, c->compute, p);
+    ev_begin(c, st, CAT_DECODE, p);
+    launch_decode(c->d, c->head, c->head64, st);
+    ev_end(c, st, p);
     c->prof.decode_launches += 1;
-    ev_begin(c, c->compute, CAT_AUX, p);
-    launch_fixup(c->d, c->head, c->sm_count, c->compute);
-    ev_end(c, c->compute, p);
+    ev_begin(c, st, CAT_AUX, p);
+    launch_fixup(c->d, c->head, c->sm_count, st);
+    ev_end(c, st, p);
     c->prof.aux_launches += 1;
     CK(cudaGetLastError());
     return M17B_OK;
 }
 
+// the trailing rounds of the previous submit (side stream) come before anything else that touches stream state
+int join_side(m17b_ctx* c)
+{
+    if (c->side_pending) {
+        CK(cudaStreamWaitEvent(c->compute, c->ev_side, 0));
+        c->side_pending = false;
+    }
+    return M17B_OK;
+}
+
 int fetch_counters(m17b_ctx* c)
 {
+    int rcj = join_side(c);
+    if (rcj != M17B_OK) return rcj;
     CK(cudaMemcpyAsync(&c->host_ctr, c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
     CK(cudaStreamSynchronize(c->compute));
     return M17B_OK;
@@ -174,6 +192,7 @@ void free_all(m17b_ctx* c)
     if (c->compute) cudaStreamSynchronize(c->compute);
     if (c->copy) cudaStreamSynchronize(c->copy);
     if (c->d2h) cudaStreamSynchronize(c->d2h);
+    if (c->side) cudaStreamSynchronize(c->side);
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
@@ -191,6 +210,9 @@ void free_all(m17b_ctx* c)
     if (c->compute) cudaStreamDestroy(c->compute);
     if (c->copy) cudaStreamDestroy(c->copy);
     if (c->d2h) cudaStreamDestroy(c->d2h);
+    if (c->side) cudaStreamDestroy(c->side);
+    if (c->ev_main) cudaEventDestroy(c->ev_main);
+    if (c->ev_side) cudaEventDestroy(c->ev_side);
     delete c;
 }
 
@@ -241,13 +263,24 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+        {
+            // highest priority: as the filter's CTAs retire, the block scheduler places the few straggler CTAs
+            // of a trailing round first (otherwise they would queue behind the whole filter launch)
+            int prio_lo = 0, prio_hi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+            CK(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi));
+        }
+        CK(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
 
         DevPtrs& d = c->d;
         d.n_streams = cfg->n_streams;
         d.np = (cfg->n_streams + 127u) & ~127u;
         // ring must hold one submit plus the lag a stream may keep plus the look-back
         // of the slow filter path / sliding DFT
-        uint32_t need = cfg->max_chunk + kRoundCap + 160 + 16;
+        // M17B_STREAMING: the next submit's filter writes its chunk while the stragglers of this one are still
+        // catching up (side stream), so a lane may be a whole chunk further behind the newest ring write
+        uint32_t need = cfg->max_chunk * ((cfg->flags & M17B_STREAMING) ? 2u : 1u) + kRoundCap + 160 + 16;
         d.ring_lines = next_pow2((need + kLine - 1) / kLine + 1);
         // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
         d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
@@ -409,15 +442,41 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     c->head64 += n;
     c->prof.scan_samples += (uint64_t) ns * n;
 
+    // Rounds.  A stream completes at most one frame per round.  M17B_STREAMING: streams walk whole frames
+    // (scan_lane's deferral), so ceil(n / 1920) rounds serve every stream in steady reception; the remaining
+    // rounds only let stragglers (acquisition, carrier-detect gaps, fix-ups) catch up.  A round costs a
+    // frame's worth of serial latency however few lanes run, so those go to the side stream, where they
+    // overlap the next submit's matched filter (which touches no per-stream scan state and writes ring
+    // positions the stragglers are past reading, see the ring guard in scan_lane).
+    const bool streaming = (c->cfg.flags & M17B_STREAMING) != 0;
     const int rounds = (int) (n / kMinFrameSpacing) + 2;
-    for (int r = 0; r != rounds; ++r) {
-        int rc = run_round(c);
+    const int main_rounds = streaming ? std::min(rounds, (int) ((n + 1919) / 1920)) : rounds;
+    {
+        int rc = join_side(c);
         if (rc != M17B_OK) return rc;
+    }
+    for (int r = 0; r != main_rounds; ++r) {
+        int rc = run_round(c, streaming, c->compute);
+        if (rc != M17B_OK) return rc;
+    }
+    cudaStream_t last = c->compute;
+    if (main_rounds < rounds) {
+        CK(cudaEventRecord(c->ev_main, c->compute));
+        CK(cudaStreamWaitEvent(c->side, c->ev_main, 0));
+        for (int r = main_rounds; r != rounds; ++r) {
+            int rc = run_round(c, streaming, c->side, c->cfg.max_chunk);
+            if (rc != M17B_OK) return rc;
+        }
+        last = c->side;
     }
     // completion snapshot of this submit: counters (incl. the record cursor) + an event
     const int slot = (int) (c->ticket % m17b_ctx::kSlots);
-    CK(cudaMemcpyAsync(&c->snap[slot], c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
-    CK(cudaEventRecord(c->done[slot], c->compute));
+    CK(cudaMemcpyAsync(&c->snap[slot], c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, last));
+    CK(cudaEventRecord(c->done[slot], last));
+    if (last == c->side) {
+        CK(cudaEventRecord(c->ev_side, c->side));
+        c->side_pending = true;
+    }
     c->ticket += 1;
     c->slot_ticket[slot] = c->ticket;
     return M17B_OK;
@@ -429,9 +488,9 @@ int m17b_sync(m17b_ctx* c)
     CK(cudaSetDevice(c->cfg.device));
     int rc = fetch_counters(c);
     if (rc != M17B_OK) return rc;
-    for (int extra = 0; c->host_ctr.lagging != 0; ++extra) {
+    for (int extra = 0; c->host_ctr.lagging != 0 || c->host_ctr.deferred != 0; ++extra) {
         if (extra == 256) { c->last_error = "streams failed to reach the head"; return M17B_ESTATE; }
-        if ((rc = run_round(c)) != M17B_OK) return rc;
+        if ((rc = run_round(c, false, c->compute)) != M17B_OK) return rc;
         if ((rc = fetch_counters(c)) != M17B_OK) return rc;
     }
     ev_collect(c);

@@ -100,6 +100,7 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
     unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
     unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
+    unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
 };
 
 struct DevPtrs {
@@ -159,7 +160,7 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
 void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);

@@ -212,8 +212,6 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
             const size_t o = ((size_t) ((p >> 5) & lmask) * d.np + s) * kLine + (p & (kLine - 1));
             float4* py = reinterpret_cast<float4*>(d.ring_y + o);
             float4* pd = reinterpret_cast<float4*>(d.ring_d + o);
-            py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
-            py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
             float dl[8];
             uint32_t raw[4];
 #pragma unroll
@@ -224,6 +222,21 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
                 int hi = __float2int_rn(__fmul_rn(row[8 * k + 2 * i + 1], 41067.0f));
                 raw[i] = ((uint32_t) lo & 0xFFFFu) | ((uint32_t) hi << 16);
             }
+            if ((int) (p - head) < 0) {
+                // the block that contains `head` of an unaligned submit: its first samples belong to the
+                // previous submit and may since have been corrected by fixup_kernel for a stream that has
+                // not consumed them yet (M17B_STREAMING) -- write the new samples only
+#pragma unroll
+                for (int i = 0; i != 8; ++i)
+                    if ((int) (p + (uint32_t) i - head) >= 0) {
+                        d.ring_y[o + i] = acc[8 * k + i];
+                        d.ring_d[o + i] = dl[i];
+                        d.ring_x[o + i] = (int16_t) ((i & 1) ? (raw[i >> 1] >> 16) : (raw[i >> 1] & 0xFFFFu));
+                    }
+                continue;
+            }
+            py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
+            py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
             pd[0] = make_float4(dl[0], dl[1], dl[2], dl[3]);
             pd[1] = make_float4(dl[4], dl[5], dl[6], dl[7]);
             *reinterpret_cast<uint4*>(d.ring_x + o) = make_uint4(raw[0], raw[1], raw[2], raw[3]);
@@ -312,7 +325,7 @@ void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned lo
 }
 
 __global__ void __launch_bounds__(kScanThreads)
-scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
+scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard)
 {
     extern __shared__ float smem[];
     float* ring_s = smem;                                  // [96][128] correlator rings
@@ -343,12 +356,12 @@ scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
     e.np = d.np;
     e.lmask = d.ring_lines - 1;
     e.s = s;
-    scan_lane(d, e, head, head64, s < d.n_streams);
+    scan_lane(d, e, head, head64, s < d.n_streams, defer != 0, guard);
 }
 
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s)
 {
-    scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head, head64);
+    scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head, head64, defer ? 1 : 0, guard);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to

@@ -933,21 +933,62 @@ M17B_FN void dcd_sums(const DevPtrs& d, const LaneIo& e, uint32_t pos, uint32_t 
     l2 = p[d.np];
 }
 
+// Offset, from the next sample the event pass handles, of the last symbol instant of the frame being
+// received (ST_FRAME): `ahead` = samples the dense pass is ahead of the event pass, so that sample sits
+// at logical correlator position corr_pos - ahead; symbols are taken when index() == sample_index, 10
+// samples apart (the dead-reckoned sample_index moves by at most +-1 a few times per frame).
+constexpr int kDeferMarginFrame = 6;
+constexpr int kDeferMarginSync = 16;
+M17B_FN int frame_end_offset(int si, int corr_pos, int ahead, int framer_index)
+{
+    int pp = corr_pos - ahead;
+    while (pp < 0) pp += 80;
+    int dsi = si - pp % 10;
+    if (dsi < 0) dsi += 10;
+    return dsi + (183 - (framer_index >> 1)) * 10;
+}
+
 // Walk this lane from its position towards `head`; on return the lane is at head, stopped on
 // a completed frame (FL_PENDING, decode_kernel's turn), waiting for a filter fix-up (FL_FIXUP)
 // or out of budget.  Called by all 32 lanes of a warp together (`valid` = the lane has a stream):
 // the block loop is warp-synchronous so that the lanes can evaluate the sync-word correlations of
 // a searching lane's block between them (corr_bit).
-M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigned long long head64, bool valid)
+M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigned long long head64, bool valid, bool defer,
+                       uint32_t guard = 0 /* samples a concurrent filter launch may be writing past head */)
 {
     uint32_t* sb = e.sb;
     uint32_t pos = valid ? sb[F_POS * 32] : head;
     uint32_t fl = valid ? sb[F_FLAGS * 32] : 0u;
     bool active = pos != head && !(fl & (FL_PENDING | FL_FIXUP));
-    if (pos != head && !active) ctr_add(&d.ctr->lagging, 1u);
+    // Deferral (rounds enqueued by m17b_submit; m17b_sync's flush rounds run every lane to the head): a lane
+    // whose current frame cannot complete before the head leaves the rest of the chunk for the next submit.
+    // The records are the same -- every frame that ends inside this chunk is still completed here -- but the
+    // lane then walks one whole frame per round together with its neighbours, instead of a partial frame
+    // after its last completion and another one at the start of the next chunk, each at half the lanes
+    // and each paying the round's serial latency (two of a submit's rounds, profiles/r01q).
+    // In ST_FRAME the end of the frame is known to +-2 samples (frame_end_offset); right after a frame, while
+    // the next sync word is awaited, only to -11 .. +5 (a re-timed sync word moves the symbol phase), hence
+    // the wider margin there -- a lane inside that margin starts walking and is stopped by the same test a
+    // few blocks later, once it is in ST_FRAME (block loop below).
+    bool deferred = false;
+    if (active && defer) {
+        const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
+        const long long left = (long long) (head - pos);
+        if (st == ST_FRAME) {
+            const uint32_t idx = sb[F_IDX * 32];
+            const int eo = frame_end_offset((int) ((fl >> FL_SI_SHIFT) & 15), (int) (idx & 0xFF),
+                                            (int) (sb[F_DPOS * 32] - pos), (int) ((idx >> 8) & 0xFFFF));
+            if ((long long) eo - kDeferMarginFrame >= left) deferred = true;
+        } else if (st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT) {
+            // sync_count counts samples from the last frame's end; frames are 1920 samples apart
+            if (1919ll - (long long) sb[F_SYNC_COUNT * 32] - kDeferMarginSync >= left) deferred = true;
+        }
+        if (deferred) active = false;
+    }
+    if (pos != head && !active && !deferred) ctr_add(&d.ctr->lagging, 1u);
     // a stream that fell so far behind that the sample ring has wrapped over what it still needs
     // (submits enqueued back to back without m17b_sync and more stops than rounds): must never happen
-    if (head - pos > d.ring_lines * (uint32_t) kLine - 176u) ctr_add(&d.ctr->faults, 1ull);
+    if (head + guard - pos > d.ring_lines * (uint32_t) kLine - 176u) ctr_add(&d.ctr->faults, 1ull);
     const bool loaded = active;
     uint32_t dpos = pos;
     uint32_t gap_r = 0;                                     // position the filter last resumed at
@@ -998,6 +1039,11 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
         int jb_e = 0, je = 0, ph0 = 0;
         bool initializing = false, go = false, need = false;
 
+        if (active && defer && z.state == ST_FRAME && head - pos < 1920u &&
+            frame_end_offset(z.si, z.corr_pos, (int) (dpos - pos), z.framer_index) - kDeferMarginFrame >= (int) (head - pos)) {
+            deferred = true;                                // this frame ends after the head: the next submit's
+            active = false;
+        }
         if (active) {
             base = pos & ~7u;
             jb_e = (int) (pos - base);
@@ -1118,7 +1164,10 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
             active = pos != head && !z.pending && budget > 0;
         }
     }
-    if (!loaded) return;
+    if (!loaded) {
+        if (deferred) ctr_add(&d.ctr->deferred, 1u);
+        return;
+    }
 
     // write back
     sb[F_POS * 32] = pos;
@@ -1157,7 +1206,8 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
         else if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) kind = 2;
         d.dec_list[(size_t) kind * d.np + ctr_add(&d.ctr->dec_count[kind], 1u)] = e.s;
     }
-    if (pos != head) ctr_add(&d.ctr->lagging, 1u);
+    if (deferred) ctr_add(&d.ctr->deferred, 1u);
+    else if (pos != head) ctr_add(&d.ctr->lagging, 1u);
 }
 
 // Fresh-demodulator state of one lane: the member initialisers of M17Demodulator

@@ -8,7 +8,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
-FIR_FMA, INVERT, PROFILE = 0x1, 0x2, 0x4
+FIR_FMA, INVERT, PROFILE, STREAMING = 0x1, 0x2, 0x4, 0x8
 HOST, DEVICE = 0, 1
 
 FRAME_DTYPE = np.dtype([

@@ -77,10 +77,11 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
 }
 
-void round(Emu& m)
+void round(Emu& m, bool defer)
 {
     DevPtrs& d = m.d;
     m.ctr.lagging = 0;
+    m.ctr.deferred = 0;
     m.ctr.fix_count = 0;
     for (int k = 0; k != 5; ++k) m.ctr.dec_count[k] = 0;
     float ring[kRing], lim[8];
@@ -92,7 +93,7 @@ void round(Emu& m)
         e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
         e.ring_y = d.ring_y; e.ring_d = d.ring_d; e.ring_x = d.ring_x;
         e.np = d.np; e.lmask = d.ring_lines - 1; e.s = s;
-        scan_lane(d, e, m.head, m.head64, true);
+        scan_lane(d, e, m.head, m.head64, true, defer);
     }
     uint16_t hist[244];
     for (int k = 0; k != 5; ++k)
@@ -109,6 +110,8 @@ extern "C" {
 long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t stride, const uint32_t* chunk_sizes,
                   size_t n_chunk_sizes, int invert, m17b_frame* out, size_t cap)
 {
+    const bool streaming = (invert & 2) != 0;
+    invert &= 1;
     uint32_t max_chunk = 0;
     for (size_t i = 0; i != n_chunk_sizes; ++i) max_chunk = std::max(max_chunk, chunk_sizes[i]);
     Emu m;
@@ -147,11 +150,17 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
         for (uint32_t s = 0; s != d.n_streams; ++s) { dcd_lane(d, s, 0, m.head, c, m.head64); dcd_lane(d, s, 1, m.head, c, m.head64); }
         m.head += c; m.head64 += c; off += c;
         int rounds = (int) (c / kMinFrameSpacing) + 2;
-        for (int r = 0; r != rounds; ++r) round(m);
+        // flags bit 1 = M17B_STREAMING: lanes may leave a partial frame for the next submit; only the
+        // final flush (m17b_sync) brings every lane to the head
+        for (int r = 0; r != rounds; ++r) round(m, streaming);
         for (int extra = 0; m.ctr.lagging != 0; ++extra) {
             if (extra == 256) return -1;
-            round(m);
+            round(m, streaming);
         }
+    }
+    for (int extra = 0; m.ctr.lagging != 0 || m.ctr.deferred != 0; ++extra) {
+        if (extra == 256) return -1;
+        round(m, false);
     }
     if (m.ctr.dropped || m.ctr.faults) return -2;
     size_t k = std::min<size_t>(m.ctr.rec_count, cap);

@@ -21,7 +21,7 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
-def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None) -> list[np.ndarray]:
+def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, streaming: bool = False) -> list[np.ndarray]:
     """Run the emulated scan/decode lanes over [n_streams, n] int16 fed in submits of the given sizes."""
     from m17_cxx_demod_b200.demod import FRAME_DTYPE, split_by_stream
     samples = np.ascontiguousarray(samples, dtype=np.int16)
@@ -30,7 +30,7 @@ def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None) -> 
     cap = ns * (2 * (n // 1600 + 2) + 8)
     out = np.zeros(cap, dtype=FRAME_DTYPE)
     k = lib().m17emu_demod(samples.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(ns), ctypes.c_size_t(n), ctypes.c_size_t(n),
-                           cs.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(cs)), ctypes.c_int(int(invert)),
+                           cs.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(cs)), ctypes.c_int(int(invert) | (2 if streaming else 0)),
                            out.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(cap))
     if k < 0:
         raise RuntimeError(f"m17emu_demod failed: {k}")

@@ -204,3 +204,28 @@ def test_pipelined_drain_upto_delivers_the_same_records():
         got = m.demod.split_by_stream(np.concatenate(parts), 70)
     assert c.faults == 0 and c.dropped == 0
     assert_records_match(want, got, "pipelined")
+
+
+@pytest.mark.parametrize("chunk", [9600, 4800, 2500])
+def test_streaming_mode_whole_frame_deferral(chunk):
+    """M17B_STREAMING: between submits a stream may trail the head by a partial frame.  Every frame that ends
+    inside a submit must still arrive with that submit's ticket, and the records must equal the oracle's."""
+    n = 96000
+    x = gen.generate(random_params(21, gen.MIXED, 96), n)
+    want, _ = ol.demod_batch("port", x)
+    with m.Demodulator(96, 9600, flags=m.STREAMING) as d:
+        parts, prev, ends = [], None, []
+        for o in range(0, n, chunk):
+            d.submit(np.ascontiguousarray(x[:, o:o + chunk]))
+            t = d.ticket()
+            if prev is not None:
+                r = d.drain_upto(prev[0])
+                # delivered with its own submit: nothing older than the previous submit's first sample
+                assert len(r) == 0 or int(r["sample_pos"].min()) >= prev[1]
+                parts.append(r)
+            prev = (t, o)
+        parts.append(d.drain())
+        c = d.counters()
+        got = m.demod.split_by_stream(np.concatenate(parts), 96)
+    assert c.faults == 0 and c.dropped == 0
+    assert_records_match(want, got, f"streaming chunk {chunk}")

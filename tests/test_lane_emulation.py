@@ -41,6 +41,16 @@ def test_emulated_lanes_ragged_submits():
     check(want, got, "ragged")
 
 
+@pytest.mark.parametrize("mode", [gen.STREAM, gen.MIXED])
+def test_emulated_lanes_streaming_deferral(mode):
+    """M17B_STREAMING: lanes leave partial frames for the next submit; records must not change."""
+    x = gen.generate(random_params(300 + mode, mode, 16), 96000)
+    want, _ = ol.demod_batch("port", x)
+    for chunks in ([9600], [4800], [1920, 3000, 7777]):
+        got = emu_lib.demod(x, chunks, streaming=True)
+        check(want, got, f"streaming mode {mode} chunks {chunks}")
+
+
 def test_emulated_lanes_idle_and_zero_inputs():
     rng = np.random.default_rng(3)
     x = np.zeros((4, 30000), np.int16)
