@@ -275,7 +275,7 @@ def main():
     totals = gather_counters({"frames": n_frames, "samples": channels * K * T}, world, dev if world > 1 else None)
 
     value = totals["samples"] / t_max / 1e6
-    # Roofline probe.  In M17B_STREAMING mode the catch-up rounds of step k share the SMs with the matched filter
+    # Roofline probe.  In M17B_STREAMING mode the rounds of step k share the SMs with the matched filter
     # of step k+1, so the filter's in-step launch time includes that time-sharing.  Three more submits, each
     # followed by m17b_sync, time the same launch (same shapes, same resident data) with nothing else running.
     fir_in_step_ms = prof.fir_ms / max(1, prof.fir_launches)
@@ -310,7 +310,7 @@ def main():
                      "timing": "CUDA events around 3 fir_kernel launches run alone right after the timed region (same shapes and data)",
                      "in_step": {"avg_launch_ms": fir_in_step_ms,
                                  "frac": (achieved * fir_ms_per_launch / fir_in_step_ms / fp32_peak) if fp32_peak and fir_in_step_ms else None,
-                                 "note": "inside the timed steps the launch shares the SMs with the previous step's catch-up scan rounds (side stream)"},
+                                 "note": "inside the timed steps the launch shares the SMs with the previous step's scan / decode rounds (M17B_STREAMING runs the sample front end of step k+1 on its own stream under the rounds of step k)"},
                      # the bit-identical filter must round the product and the sum separately: a multiply and an
                      # add per tap instead of one FFMA, i.e. at most half the FFMA-counted peak.  Measured here
                      # with the same instruction mix (FMUL+FADD, and 2 FMUL + 1 packed FADD2 as the kernel issues).

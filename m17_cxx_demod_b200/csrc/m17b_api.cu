@@ -34,11 +34,12 @@ struct m17b_ctx {
     cudaEvent_t stage_free[2] = {nullptr, nullptr}, stage_ready[2] = {nullptr, nullptr};
     int cur_stage = 0;
     cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;   // kernels; sample H2D; record D2H
-    // M17B_STREAMING: the catch-up rounds of a submit (after its whole-frame rounds) run on `side`, under the
-    // matched filter of the next submit; ev_side marks their end
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_main = nullptr, ev_side = nullptr;
-    bool side_pending = false;
+    // M17B_STREAMING: the sample front end of submit k+1 (filter, tail, carrier-detect pre-pass) runs on `front`
+    // while the rounds of submit k run on `compute`; ev_front = front end of the newest submit done,
+    // ev_rounds[k & 1] = rounds of submit k done (the front end may be one submit ahead, not two)
+    cudaStream_t front = nullptr;
+    cudaEvent_t ev_front = nullptr, ev_rounds[2] = {nullptr, nullptr};
+    unsigned long long n_submits = 0;
     uint32_t head = 0;
     unsigned long long head64 = 0;
     int sm_count = 0;
@@ -131,20 +132,8 @@ int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard = 0)
     return M17B_OK;
 }
 
-// the trailing rounds of the previous submit (side stream) come before anything else that touches stream state
-int join_side(m17b_ctx* c)
-{
-    if (c->side_pending) {
-        CK(cudaStreamWaitEvent(c->compute, c->ev_side, 0));
-        c->side_pending = false;
-    }
-    return M17B_OK;
-}
-
 int fetch_counters(m17b_ctx* c)
 {
-    int rcj = join_side(c);
-    if (rcj != M17B_OK) return rcj;
     CK(cudaMemcpyAsync(&c->host_ctr, c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
     CK(cudaStreamSynchronize(c->compute));
     return M17B_OK;
@@ -192,7 +181,7 @@ void free_all(m17b_ctx* c)
     if (c->compute) cudaStreamSynchronize(c->compute);
     if (c->copy) cudaStreamSynchronize(c->copy);
     if (c->d2h) cudaStreamSynchronize(c->d2h);
-    if (c->side) cudaStreamSynchronize(c->side);
+    if (c->front) cudaStreamSynchronize(c->front);
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
@@ -210,9 +199,9 @@ void free_all(m17b_ctx* c)
     if (c->compute) cudaStreamDestroy(c->compute);
     if (c->copy) cudaStreamDestroy(c->copy);
     if (c->d2h) cudaStreamDestroy(c->d2h);
-    if (c->side) cudaStreamDestroy(c->side);
-    if (c->ev_main) cudaEventDestroy(c->ev_main);
-    if (c->ev_side) cudaEventDestroy(c->ev_side);
+    if (c->front) cudaStreamDestroy(c->front);
+    if (c->ev_front) cudaEventDestroy(c->ev_front);
+    for (auto& e : c->ev_rounds) if (e) cudaEventDestroy(e);
     delete c;
 }
 
@@ -260,18 +249,18 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, cfg->device));
         c->sm_count = prop.multiProcessorCount;
-        CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
         {
-            // highest priority: as the filter's CTAs retire, the block scheduler places the few straggler CTAs
-            // of a trailing round first (otherwise they would queue behind the whole filter launch)
+            // the rounds are a chain of latency-bound launches: highest priority, so that their CTAs are placed
+            // as soon as CTAs of a concurrent filter launch (front stream, M17B_STREAMING) retire
             int prio_lo = 0, prio_hi = 0;
             CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-            CK(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi));
+            CK(cudaStreamCreateWithPriority(&c->compute, cudaStreamNonBlocking, prio_hi));
+            CK(cudaStreamCreateWithPriority(&c->front, cudaStreamNonBlocking, prio_lo));
+            CK(cudaEventCreateWithFlags(&c->ev_front, cudaEventDisableTiming));
+            for (auto& e : c->ev_rounds) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
-        CK(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
+        CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
 
         DevPtrs& d = c->d;
         d.n_streams = cfg->n_streams;
@@ -389,6 +378,13 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     const int16_t* dev_in = samples;
     size_t dev_stride = stride;
     EvPair p{};
+    // M17B_STREAMING: the sample front end (filter, tail, carrier-detect pre-pass) has its own stream and runs
+    // while the rounds of the previous submit are still going: it touches no scan state, and with the ring
+    // doubled it writes no ring position a lane of the previous submit still reads (ring guard in scan_lane).
+    // It may be one submit ahead of the rounds, not two.
+    const bool streaming = (c->cfg.flags & M17B_STREAMING) != 0;
+    cudaStream_t fs = streaming ? c->front : c->compute;
+    if (streaming) CK(cudaStreamWaitEvent(fs, c->ev_rounds[c->n_submits & 1], 0));     // rounds of submit k-2
     if (location == M17B_HOST) {
         int b = c->cur_stage;
         c->cur_stage ^= 1;
@@ -402,33 +398,30 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
                                  n * sizeof(int16_t), ns, cudaMemcpyHostToDevice, c->copy));
         ev_end(c, c->copy, p);
         CK(cudaEventRecord(c->stage_ready[b], c->copy));
-        CK(cudaStreamWaitEvent(c->compute, c->stage_ready[b], 0));
+        CK(cudaStreamWaitEvent(fs, c->stage_ready[b], 0));
         c->prof.h2d_bytes += (uint64_t) ns * n * sizeof(int16_t);
         dev_in = c->stage[b];
         dev_stride = n;
-        // after the kernels below
+    }
+    {
         const bool invert = c->cfg.flags & M17B_INVERT;
-        ev_begin(c, c->compute, CAT_FIR, p);
-        launch_fir(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->head, c->cfg.flags & M17B_FIR_FMA, invert, c->compute);
-        ev_end(c, c->compute, p);
-        ev_begin(c, c->compute, CAT_AUX, p);
-        launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], c->compute);
-        ev_end(c, c->compute, p);
-        CK(cudaEventRecord(c->stage_free[b], c->compute));
-    } else {
-        const bool invert = c->cfg.flags & M17B_INVERT;
-        ev_begin(c, c->compute, CAT_FIR, p);
-        launch_fir(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->head, c->cfg.flags & M17B_FIR_FMA, invert, c->compute);
-        ev_end(c, c->compute, p);
-        ev_begin(c, c->compute, CAT_AUX, p);
-        launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], c->compute);
-        ev_end(c, c->compute, p);
+        ev_begin(c, fs, CAT_FIR, p);
+        launch_fir(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->head, c->cfg.flags & M17B_FIR_FMA, invert, fs);
+        ev_end(c, fs, p);
+        ev_begin(c, fs, CAT_AUX, p);
+        launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], fs);
+        ev_end(c, fs, p);
+        if (location == M17B_HOST) CK(cudaEventRecord(c->stage_free[c->cur_stage ^ 1], fs));
     }
     // carrier-detect pre-pass over the new samples (reads ring_d written by the filter)
-    ev_begin(c, c->compute, CAT_DCD, p);
-    launch_dcd(c->d, c->head, (uint32_t) n, c->head64, c->compute);
-    ev_end(c, c->compute, p);
+    ev_begin(c, fs, CAT_DCD, p);
+    launch_dcd(c->d, c->head, (uint32_t) n, c->head64, fs);
+    ev_end(c, fs, p);
     c->prof.dcd_launches += 1;
+    if (streaming) {
+        CK(cudaEventRecord(c->ev_front, fs));
+        CK(cudaStreamWaitEvent(c->compute, c->ev_front, 0));
+    }
     CK(cudaGetLastError());
     c->cur_tail ^= 1;
     c->prof.fir_launches += 1;
@@ -444,39 +437,19 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
 
     // Rounds.  A stream completes at most one frame per round.  M17B_STREAMING: streams walk whole frames
     // (scan_lane's deferral), so ceil(n / 1920) rounds serve every stream in steady reception; the remaining
-    // rounds only let stragglers (acquisition, carrier-detect gaps, fix-ups) catch up.  A round costs a
-    // frame's worth of serial latency however few lanes run, so those go to the side stream, where they
-    // overlap the next submit's matched filter (which touches no per-stream scan state and writes ring
-    // positions the stragglers are past reading, see the ring guard in scan_lane).
-    const bool streaming = (c->cfg.flags & M17B_STREAMING) != 0;
+    // rounds let stragglers (acquisition, carrier-detect gaps, fix-ups) catch up.  A round costs a frame's
+    // worth of serial latency however few lanes run; the next submit's front end fills the machine meanwhile.
     const int rounds = (int) (n / kMinFrameSpacing) + 2;
-    const int main_rounds = streaming ? std::min(rounds, (int) ((n + 1919) / 1920)) : rounds;
-    {
-        int rc = join_side(c);
+    for (int r = 0; r != rounds; ++r) {
+        int rc = run_round(c, streaming, c->compute, streaming ? c->cfg.max_chunk : 0u);
         if (rc != M17B_OK) return rc;
     }
-    for (int r = 0; r != main_rounds; ++r) {
-        int rc = run_round(c, streaming, c->compute);
-        if (rc != M17B_OK) return rc;
-    }
-    cudaStream_t last = c->compute;
-    if (main_rounds < rounds) {
-        CK(cudaEventRecord(c->ev_main, c->compute));
-        CK(cudaStreamWaitEvent(c->side, c->ev_main, 0));
-        for (int r = main_rounds; r != rounds; ++r) {
-            int rc = run_round(c, streaming, c->side, c->cfg.max_chunk);
-            if (rc != M17B_OK) return rc;
-        }
-        last = c->side;
-    }
+    if (streaming) CK(cudaEventRecord(c->ev_rounds[c->n_submits & 1], c->compute));
+    c->n_submits += 1;
     // completion snapshot of this submit: counters (incl. the record cursor) + an event
     const int slot = (int) (c->ticket % m17b_ctx::kSlots);
-    CK(cudaMemcpyAsync(&c->snap[slot], c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, last));
-    CK(cudaEventRecord(c->done[slot], last));
-    if (last == c->side) {
-        CK(cudaEventRecord(c->ev_side, c->side));
-        c->side_pending = true;
-    }
+    CK(cudaMemcpyAsync(&c->snap[slot], c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaEventRecord(c->done[slot], c->compute));
     c->ticket += 1;
     c->slot_ticket[slot] = c->ticket;
     return M17B_OK;

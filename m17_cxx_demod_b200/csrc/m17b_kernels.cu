@@ -18,6 +18,8 @@
 #include "m17b_dev.cuh"
 
 #include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 
 namespace m17b {
 
