@@ -1,15 +1,18 @@
 // m17b_api.cu -- host context behind the C ABI in include/m17b.h.
 //
-// One context = one GPU = N resident streams.  m17b_submit() enqueues, on the
-// context's compute stream,
+// One context = one GPU = N resident streams.  m17b_submit() enqueues
 //     [H2D copy on the copy stream, double buffered]        (host input only)
 //     fir_kernel over the new samples -> sample ring          (kernel A)
 //     tail_kernel (keeps 160 raw samples of filter history)
-//     R rounds of { scan_kernel ; decode_kernel }             (kernels B, C)
+//     dcd_kernel (carrier-detect pre-pass -> window sums)     (kernel A2)
+//     R rounds of { scan_kernel ; decode_kernel ; fixup_kernel }   (kernels B, C)
 // where a round lets every stream advance to its next completed frame (or by at
 // most kRoundCap samples).  Frame completions of one stream are >= 1600 samples
 // apart, so R = n/1600 + 2 rounds always reach the head; m17b_sync() verifies
-// that on the device (`lagging`) and adds rounds if it ever is not so.
+// that on the device (`lagging`, `deferred`) and adds rounds if it ever is not so.
+// Streams: `compute` (rounds; everything without M17B_STREAMING), `front` (filter,
+// tail, pre-pass of the next submit under the rounds of the current one, with
+// M17B_STREAMING), `copy` (sample upload), `d2h` (record read-back).
 #include "m17b_dev.cuh"
 
 #include <algorithm>
@@ -267,8 +270,8 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         d.np = (cfg->n_streams + 127u) & ~127u;
         // ring must hold one submit plus the lag a stream may keep plus the look-back
         // of the slow filter path / sliding DFT
-        // M17B_STREAMING: the next submit's filter writes its chunk while the stragglers of this one are still
-        // catching up (side stream), so a lane may be a whole chunk further behind the newest ring write
+        // M17B_STREAMING: the next submit's filter writes its chunk while the lanes of this one are still
+        // running their rounds (front stream), so a lane may be a whole chunk further behind the newest ring write
         uint32_t need = cfg->max_chunk * ((cfg->flags & M17B_STREAMING) ? 2u : 1u) + kRoundCap + 160 + 16;
         d.ring_lines = next_pow2((need + kLine - 1) / kLine + 1);
         // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
