@@ -46,6 +46,21 @@ def fir_traffic(channels, chunk, fma):
     return t["dram_bytes_read"] + t["dram_bytes_write"]
 
 
+def bind_to_gpu_numa_node(index):
+    """Run this rank (and first-touch its pinned staging buffers) on the CPUs NVML reports as local to its GPU, so
+    that N ranks uploading at once do not all cross the same inter-socket link.  No-op when NVML gives no answer."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        n_cpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(index), (n_cpu + 63) // 64)
+        cpus = {i for i in range(n_cpu) if (mask[i // 64] >> (i % 64)) & 1} & os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -197,6 +212,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    if world > 1:
+        bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
@@ -351,7 +368,13 @@ def main():
     del d
     # ---- e2e: same call sequence from pinned host memory --------------------------------------
     if not args.no_e2e:
-        Ke = max(1, args.e2e_steps if world == 1 else min(args.e2e_steps, 4))   # bounds pinned host memory per rank
+        Ke = max(1, args.e2e_steps)
+        try:                                                   # bound the pinned host memory of all ranks to a quarter of what is free
+            import psutil
+            budget = psutil.virtual_memory().available // 4 // max(1, world)
+            Ke = max(2, min(Ke, int(budget // (channels * T * 2)) - 2))
+        except ImportError:
+            Ke = Ke if world == 1 else min(Ke, 4)
         NW = 2                                                 # untimed warm-up submits (one per staging buffer)
         if (Ke + NW) * T > total:
             Ke = total // T - NW
