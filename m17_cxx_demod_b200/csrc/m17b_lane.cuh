@@ -1284,20 +1284,41 @@ M17B_FN_COLD uint32_t crc16_lsf(const uint8_t* lsf, size_t np)
     return reg;
 }
 
-// One depunctured soft bit through the folded derandomise/deinterleave map.
-M17B_FN int soft_bit(const int16_t* llr, size_t np, int m, int stale)
+// One depunctured soft bit through the folded derandomise/deinterleave map, in two halves so that the
+// loads of a whole block of trellis steps can be issued before the first one is used.
+// branch-free: the load is issued unconditionally (slot 0 for an erasure / the stale element)
+M17B_FN int soft_index(int m)
 {
-    // branch-free: the load is issued unconditionally (slot 0 for an erasure / the stale element), so
-    // the 16 soft bits of a block of trellis steps are 16 independent loads in flight; with early
-    // returns every call was a branch region and the loads were serialised (40 % of decode_kernel's
-    // stall samples, profiles/r01j)
     const bool special = m == 0 || m == kMapStale;
-    const int k = special ? 0 : (m < 0 ? -m : m) - 1;
-    const int pair = llr[(size_t) (k >> 1) * np];
+    return special ? 0 : (m < 0 ? -m : m) - 1;
+}
+
+M17B_FN int load_pair(const int16_t* p)
+{
+#ifdef __CUDACC__
+    // volatile: ptxas otherwise sinks each load to just before its use (register pressure), which exposes
+    // a full L2 latency in front of every add-compare-select step (45 % of decode_kernel's stall samples,
+    // profiles/r01z); in program order all loads of a block are in flight together
+    int v;
+    asm volatile("ld.global.s16 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+#else
+    return *p;
+#endif
+}
+
+M17B_FN int soft_finish(int m, int k, int pair, int stale)
+{
     int v = (k & 1) ? (int) (int8_t) (pair >> 8) : (int) (int8_t) (pair & 0xFF);
     v = m < 0 ? -v : v;
     v = m == 0 ? 0 : v;
     return m == kMapStale ? stale : v;
+}
+
+M17B_FN int soft_bit(const int16_t* llr, size_t np, int m, int stale)
+{
+    const int k = soft_index(m);
+    return soft_finish(m, k, llr[(size_t) (k >> 1) * np], stale);
 }
 
 // butterfly J: cost_[J][0] = +7 iff bit 2 of J, cost_[J][1] = +7 iff bit0 ^ bit1 of J
@@ -1334,10 +1355,14 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
     // a handful of warps per SM, one frame per thread).
     constexpr int kBlk = 8;
     for (int tb = 0; tb < steps; tb += kBlk) {
-        int sbit[2 * kBlk];
+        int sbit[2 * kBlk], sm[2 * kBlk];
 #pragma unroll
-        for (int u = 0; u != 2 * kBlk; ++u)
-            sbit[u] = 2 * tb + u < n_in ? soft_bit(llr, np, map[2 * tb + u], stale) : 0;
+        for (int u = 0; u != 2 * kBlk; ++u) {
+            sm[u] = 2 * tb + u < n_in ? map[2 * tb + u] : 0;
+            sbit[u] = load_pair(llr + (size_t) (soft_index(sm[u]) >> 1) * np);
+        }
+#pragma unroll
+        for (int u = 0; u != 2 * kBlk; ++u) sbit[u] = soft_finish(sm[u], soft_index(sm[u]), sbit[u], stale);
 #pragma unroll
         for (int u = 0; u != kBlk; ++u) {
             const int t = tb + u;
