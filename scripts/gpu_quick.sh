@@ -10,5 +10,5 @@ print({k:d[k] for k in ["value","ms_per_step","kernel_ms_per_step","parity","roo
 print(d.get("e2e"))
 PY
 if [ "$2" = "ncu" ]; then
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|fir_kernel|decode_kernel|dcd_kernel' -s 180 -c 18 -o gpurun_out/${tag}_steady python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu.log 2>&1; echo "ncu exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|fir_kernel|decode_kernel|dcd_kernel|fixup_kernel' -s 270 -c 27 -o gpurun_out/${tag}_steady python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu.log 2>&1; echo "ncu exit $?"
 fi
