@@ -76,6 +76,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="diagnostic: wait for every step's own records before the next submit (no step overlaps the next)")
     ap.add_argument("--ref-streams", type=int, default=1024, help="streams per step of the reference arm")
     return ap.parse_args()
 
@@ -267,6 +269,11 @@ def main():
     for k in range(W, W + K):
         d.submit_device(big.data_ptr() + 2 * k * T, T, total)
         t_k = d.ticket()
+        if args.no_overlap:
+            r = d.drain_upto(t_k)
+            n_frames += len(r)
+            records.append(r)
+            continue
         if prev is not None:
             r = d.drain_upto(prev)
             n_frames += len(r)
@@ -318,7 +325,7 @@ def main():
                    "l2": f"inputs larger than L2 ({channels * T * 2 / 1e6:.0f} MB of int16 per step, never re-read)",
                    "drain": "records of step k read back (m17b_drain_upto) while step k+1 runs; all inside the timed region",
                    "mode": "M17B_STREAMING (streams walk whole frames; every frame ending in a step is delivered with that step)",
-                   "generator_s": round(gen_s, 2)},
+                   "generator_s": round(gen_s, 2), **({"no_overlap": True} if args.no_overlap else {})},
         "frames_per_s": totals["frames"] / t_max, "wall_s": t_wall, "device_s": t_dev,
         "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": achieved / fp32_peak if fp32_peak else None, "traffic": fir_traffic(channels, T, args.fma),
