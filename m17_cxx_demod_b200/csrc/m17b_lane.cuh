@@ -802,6 +802,30 @@ M17B_FN void load_chunk(Chunk& c, const LaneIo& e, uint32_t base)
 M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base)
 {
     if (!clocked) return;               // :675-689: the filter and the correlator are not clocked while !dcd_
+    if (jb == 0 && je == 8 && z.rp <= kRing - 8) {
+        // whole block, no ring wrap inside it: same arithmetic without the per-sample bookkeeping
+        float h1 = z.iir0, h2 = z.iir1;
+        float* ring = e.ring + z.rp * RS;
+#pragma unroll
+        for (int j = 0; j != 8; ++j) {
+            float h0 = fabsf(c.y[j]);
+            h0 -= -1.98148851f * h1;
+            h0 -= 0.98165828f * h2;
+            float r = 0.f;
+            r += 4.24433681e-05f * h0;
+            r += 8.48867363e-05f * h1;
+            r += 4.24433681e-05f * h2;
+            ring[j * RS] = c.y[j];
+            e.lim[j * RS] = r;
+            h2 = h1; h1 = h0;
+            if (j == 7) z.limit = r;
+        }
+        z.iir0 = h1; z.iir1 = h2;
+        z.gap_k = z.gap_k + 8 < kTapsUsed ? z.gap_k + 8 : kTapsUsed;
+        z.rp = z.rp == kRing - 8 ? 0 : z.rp + 8;
+        z.corr_pos = z.corr_pos >= 72 ? z.corr_pos - 72 : z.corr_pos + 8;
+        return;
+    }
 #pragma unroll
     for (int j = 0; j != 8; ++j) {
         if (j < jb || j >= je) continue;
