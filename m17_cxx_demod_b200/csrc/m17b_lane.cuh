@@ -361,7 +361,13 @@ M17B_FN_COLD void take_snapshot(float* snap, const int16_t* ring_x, uint32_t np,
 // binary-searches 43 thresholds spaced ~1/7 apart; the same lower_bound index is found here
 // from an arithmetic first guess corrected against the thresholds themselves (a copy of the
 // table in shared memory: lanes look up different entries).
-struct LlrTable { float thr[44]; uint32_t val[44]; };
+struct LlrTable { float thr[48]; uint32_t val[44]; };      // thr[i + 2] = threshold i; -inf below, +inf above
+
+// entry `i` (0..47) of the padded threshold column
+M17B_FN float llr_thr_padded(const float* thr43, int i)
+{
+    return i < 2 ? -__builtin_huge_valf() : i < 45 ? thr43[i - 2] : __builtin_huge_valf();
+}
 
 M17B_FN uint32_t llr4(const LlrTable& tab, float sample)
 {
@@ -369,8 +375,16 @@ M17B_FN uint32_t llr4(const LlrTable& tab, float sample)
     float v = (t < 3.0f) ? t : 3.0f;                  // std::min(MAX_VALUE, t)
     int g = (int) ((v + 3.0f) * 7.0f);                // about the number of thresholds below v
     g = g < 0 ? 0 : (g > 43 ? 43 : g);
-    while (g > 0 && !(tab.thr[g - 1] < v)) --g;       // lower_bound: first index with !(thr < v)
-    while (g < 43 && tab.thr[g] < v) ++g;
+    // lower_bound = the number of thresholds below v (they increase): four independent look-ups around
+    // the guess settle it when it lies in g-1 .. g+1, which it does but for rounding at the far ends
+    const float* w = tab.thr + g;                     // thresholds g-2 .. g+1
+    const float a = w[0], b = w[1], c = w[2], d = w[3];
+    const int n = (int) (a < v) + (int) (b < v) + (int) (c < v) + (int) (d < v);
+    if (n >= 1 && n <= 3) g = g - 2 + n;
+    else {
+        while (g > 0 && !(tab.thr[g + 1] < v)) --g;   // first index with !(thr < v)
+        while (g < 43 && tab.thr[g + 2] < v) ++g;
+    }
     if (g == 43) g = 42;
     return tab.val[g];
 }

@@ -45,8 +45,8 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
 {
     static bool tables = false;
     if (!tables) { build_tables(h_tab, h_golay); tables = true; }
+    for (int i = 0; i != 48; ++i) m.tab.thr[i] = llr_thr_padded(h_tab.llr_thr, i);
     for (int i = 0; i != 43; ++i) {
-        m.tab.thr[i] = h_tab.llr_thr[i];
         m.tab.val[i] = (uint32_t) (uint8_t) h_tab.llr_val[i][0] | ((uint32_t) (uint8_t) h_tab.llr_val[i][1] << 8);
     }
     DevPtrs& d = m.d;
@@ -104,6 +104,18 @@ void round(Emu& m, bool defer)
 } // namespace
 
 extern "C" {
+
+// The scan's soft-slicer look-up (llr4, m17b_lane.cuh) for n samples -> packed (second << 8 | first) pairs.
+void m17emu_llr4(const float* samples, size_t n, uint16_t* out)
+{
+    Emu m;
+    static bool tables = false;
+    if (!tables) { build_tables(h_tab, h_golay); tables = true; }
+    for (int i = 0; i != 48; ++i) m.tab.thr[i] = llr_thr_padded(h_tab.llr_thr, i);
+    for (int i = 0; i != 43; ++i)
+        m.tab.val[i] = (uint32_t) (uint8_t) h_tab.llr_val[i][0] | ((uint32_t) (uint8_t) h_tab.llr_val[i][1] << 8);
+    for (size_t i = 0; i != n; ++i) out[i] = (uint16_t) llr4(m.tab, samples[i]);
+}
 
 // Demodulate [n_streams][n] int16 (row stride `stride`) fed in submits of the given sizes (cycled).
 // Returns the number of records written to out (stream-major order is NOT guaranteed; seq is).

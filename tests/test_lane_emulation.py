@@ -60,3 +60,25 @@ def test_emulated_lanes_idle_and_zero_inputs():
     want, _ = ol.demod_batch("port", x)
     got = emu_lib.demod(x, [30000])
     check(want, got, "idle")
+
+
+def test_soft_slicer_lookup_matches_oracle():
+    """llr4 (four look-ups around an arithmetic guess) against the oracle's binary search (Util.h:128-145):
+    a dense sweep of [-3.2, 3.2], every threshold with its neighbouring floats, specials."""
+    import ctypes
+    port = ol.port()
+    thr = np.zeros(43, np.float32); pairs = np.zeros(86, np.int8)
+    port.m17port_llr_table(thr.ctypes.data_as(ctypes.c_void_p), pairs.ctypes.data_as(ctypes.c_void_p))
+    near = np.concatenate([np.nextafter(thr, np.float32(-9)), thr, np.nextafter(thr, np.float32(9))])
+    for _ in range(3):
+        near = np.concatenate([near, np.nextafter(near, np.float32(-9)), np.nextafter(near, np.float32(9))])
+    x = np.concatenate([np.linspace(-3.2, 3.2, 400001).astype(np.float32), near.astype(np.float32),
+                        np.array([0.0, -0.0, 3.0, -3.0, 1e9, -1e9, np.inf, -np.inf], np.float32)])
+    got = np.zeros(len(x), np.uint16)
+    emu_lib.lib().m17emu_llr4(x.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(x)), got.ctypes.data_as(ctypes.c_void_p))
+    want = np.zeros((len(x), 2), np.int8)
+    port.m17port_llr.argtypes = [ctypes.c_float, ctypes.c_void_p]
+    for i, s in enumerate(x):
+        port.m17port_llr(float(s), want[i].ctypes.data_as(ctypes.c_void_p))
+    w16 = want.view(np.uint8).astype(np.uint16)
+    assert np.array_equal(got, w16[:, 0] | (w16[:, 1] << 8))
