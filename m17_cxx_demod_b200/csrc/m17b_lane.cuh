@@ -620,9 +620,8 @@ M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, bool bert)
 }
 
 // M17Demodulator.h:595-654 up to the decoder call (which decode_kernel performs)
-M17B_FN void do_frame(Scan& z, const LaneIo& e)
+M17B_FN void do_frame(Scan& z, const LaneIo& e, int idx /* index() of this sample = pp % 10 */)
 {
-    int idx = z.pp % 10;
     int diff = z.si - idx;
     if (diff == 5 || diff == -5) {
         // ClockRecovery.h:76-88
@@ -754,10 +753,10 @@ M17B_FN bool corr_bit(const float* ring, const float* lim, int ph0, int t)
 
 // One sample of M17Demodulator.h:695-740 (everything between correlator.sample()
 // and the carrier-detect cadence check).
-M17B_FN void event_step(Scan& z, const LaneIo& e)
+M17B_FN void event_step(Scan& z, const LaneIo& e, int i10 /* z.pp % 10 */)
 {
     uint32_t* sb = e.sb;
-    if (z.pp % 10 == 0) {               // :695-709
+    if (i10 == 0) {               // :695-709
         if (z.need_reset) {
             Kalman k; kf_reset(k, (float) z.ssi);          // ClockRecovery.h:33-39
             kf_store(sb, F_CK_X0, k);
@@ -779,7 +778,7 @@ M17B_FN void event_step(Scan& z, const LaneIo& e)
 
     switch (z.state) {                  // :714-740
     case ST_UNLOCKED: do_unlocked(z, e); break;
-    case ST_LSF_SYNC: if (z.pp % 10 == z.si) do_lsf_sync(z, e); break;
+    case ST_LSF_SYNC: if (i10 == z.si) do_lsf_sync(z, e); break;
     case ST_STREAM_SYNC:
         z.sync_count += 1;
         if (z.sync_count >= 78) do_stream_sync(z, e);
@@ -796,7 +795,7 @@ M17B_FN void event_step(Scan& z, const LaneIo& e)
         if (z.sync_count < 86) z.sync_count += 1;
         else { z.need_update = true; z.state = ST_FRAME; }
         break;
-    default: do_frame(z, e); break;
+    default: do_frame(z, e, i10); break;
     }
 }
 
@@ -1155,18 +1154,21 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                 int back = (int) (dpos - base) - j;         // >= 1
                 z.pp = z.corr_pos - back; if (z.pp < 0) z.pp += 80;
                 z.ph = z.rp - back; if (z.ph < 0) z.ph += kRing;
+                int i10 = z.pp % 10;                        // index() of block sample j, kept in step with z.pp
                 while (j < je) {
-                    int q = quiet_samples(z, z.pp % 10, j, masks);
+                    int q = quiet_samples(z, i10, j, masks);
                     if (q >= je - j) { advance_quiet(z, je - j); j = je; break; }
                     if (q) {
                         advance_quiet(z, q);
                         j += q;
                         z.pp += q; if (z.pp >= 80) z.pp -= 80;
                         z.ph += q; if (z.ph >= kRing) z.ph -= kRing;
+                        i10 += q; if (i10 >= 10) i10 -= 10;
                     }
                     z.limit = e.lim[j * RS];
-                    event_step(z, e);
+                    event_step(z, e, i10);
                     ++j;
+                    i10 = i10 == 9 ? 0 : i10 + 1;
                     z.pp = z.pp == 79 ? 0 : z.pp + 1;
                     z.ph = z.ph == kRing - 1 ? 0 : z.ph + 1;
                     if (z.pending) break;
