@@ -334,9 +334,9 @@ scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint
     float* lim_s = smem + kRing * kScanThreads;            // [8][128] per-sample limits of the current block
     LlrTable* tab = reinterpret_cast<LlrTable*>(smem + (kRing + 8) * kScanThreads);
     const int tid = threadIdx.x;
-    if (tid < 48) tab->thr[tid] = llr_thr_padded(c_tab.llr_thr, tid);
-    if (tid < 43) {
-        tab->val[tid] = (uint32_t) (uint8_t) c_tab.llr_val[tid][0] | ((uint32_t) (uint8_t) c_tab.llr_val[tid][1] << 8);
+    for (int i = tid; i < 48; i += kScanThreads) tab->thr[i] = llr_thr_padded(c_tab.llr_thr, i);
+    for (int i = tid; i < 43; i += kScanThreads) {
+        tab->val[i] = (uint32_t) (uint8_t) c_tab.llr_val[i][0] | ((uint32_t) (uint8_t) c_tab.llr_val[i][1] << 8);
     }
     __syncthreads();
     const uint32_t s = blockIdx.x * kScanThreads + tid;      // < np: padded lanes stay in the warp as helpers
