@@ -1379,6 +1379,27 @@ M17B_FN void butterfly(const int (&m)[16], int (&n)[16], uint32_t& hist, int a0,
     n[2 * J + 1] = d1 ? m3 : m1;
 }
 
+#ifdef __CUDACC__
+// Two states per register: the path metrics fit 16 bits (at most 244 steps x 28, and 16,000 stands in for the
+// INT_MAX / 2 of the states a frame cannot start in: such a path still loses to every real one and compares
+// with its like exactly as before).  Butterfly J reads states J and J + 8, each broadcast to both halves, adds
+// the branch costs (cost0, cost1) / (cost1, cost0) and keeps the smaller: the halves of the result are the new
+// states 2J and 2J + 1, and "old path from J + 8 wins" is Viterbi.h:148-149's strict m0 > m2, the complement
+// of the a <= b predicate the packed minimum returns.
+template <int J>
+M17B_FN void butterfly2(const uint32_t (&m)[8], uint32_t (&n)[8], uint32_t& hist, uint32_t c01, uint32_t c10)
+{
+    const uint32_t p0 = __byte_perm(m[J >> 1], 0, (J & 1) ? 0x3232 : 0x1010);
+    const uint32_t p1 = __byte_perm(m[(J + 8) >> 1], 0, (J & 1) ? 0x3232 : 0x1010);
+    const uint32_t x = p0 + c01;                               // (m0, m1): halves stay below 2^15, no carry across
+    const uint32_t y = p1 + c10;                               // (m2, m3)
+    bool le_hi, le_lo;
+    n[J] = __vibmin_s16x2(x, y, &le_hi, &le_lo);
+    hist |= (le_lo ? 0u : 1u) << (2 * J);
+    hist |= (le_hi ? 0u : 1u) << (2 * J + 1);
+}
+#endif
+
 // Viterbi.h:181-236.  Writes out_bits(kind) bits MSB-first into out[] (to_byte_array,
 // Util.h:300-318) and returns round(min_metric / 7.f).
 M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale,
@@ -1386,10 +1407,17 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
 {
     const int16_t* map = M17B_TAB.vmap[kind];
     const int n_in = map_len(kind), n_out = out_bits(kind), steps = n_in / 2;
+#ifdef __CUDACC__
+    uint32_t m[8], n[8];                                      // states 2i (low half) and 2i + 1 (high half)
+#pragma unroll
+    for (int i = 0; i != 8; ++i) m[i] = 16000u | (16000u << 16);
+    m[0] = 16000u << 16;
+#else
     int m[16], n[16];
 #pragma unroll
     for (int i = 0; i != 16; ++i) m[i] = 0x7fffffff / 2;
     m[0] = 0;
+#endif
     // Soft bits are fetched a block of 8 trellis steps ahead: 16 independent loads in flight instead of
     // two dependent global loads in front of every add-compare-select step (the kernel is latency-bound:
     // a handful of warps per SM, one frame per thread).
@@ -1412,6 +1440,21 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
             if (s0) { a0 = abs(7 - s0); a1 = abs(-7 - s0); }
             if (s1) { b0 = abs(7 - s1); b1 = abs(-7 - s1); }
             uint32_t h = 0;
+#ifdef __CUDACC__
+            // (cost0, cost1) of a butterfly by its two cost signs (see butterfly<J>): c0p c1p = 00 -> (a1 + b1, a0 + b0),
+            // 01 -> (a1 + b0, a0 + b1), 10 and 11 are those with the halves swapped
+            const uint32_t pa = (uint32_t) (a1 + b1) | ((uint32_t) (a0 + b0) << 16);
+            const uint32_t pb = (uint32_t) (a1 + b0) | ((uint32_t) (a0 + b1) << 16);
+            const uint32_t pd = __byte_perm(pa, 0, 0x1032), pc = __byte_perm(pb, 0, 0x1032);
+            // butterfly J: c0p = bit 2 of J, c1p = bit0 ^ bit1 of J
+            butterfly2<0>(m, n, h, pa, pd); butterfly2<1>(m, n, h, pb, pc);
+            butterfly2<2>(m, n, h, pb, pc); butterfly2<3>(m, n, h, pa, pd);
+            butterfly2<4>(m, n, h, pc, pb); butterfly2<5>(m, n, h, pd, pa);
+            butterfly2<6>(m, n, h, pd, pa); butterfly2<7>(m, n, h, pc, pb);
+            hist_col[t * HS] = (uint16_t) h;
+#pragma unroll
+            for (int i = 0; i != 8; ++i) m[i] = n[i];
+#else
             butterfly<0>(m, n, h, a0, a1, b0, b1); butterfly<1>(m, n, h, a0, a1, b0, b1);
             butterfly<2>(m, n, h, a0, a1, b0, b1); butterfly<3>(m, n, h, a0, a1, b0, b1);
             butterfly<4>(m, n, h, a0, a1, b0, b1); butterfly<5>(m, n, h, a0, a1, b0, b1);
@@ -1419,12 +1462,22 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
             hist_col[t * HS] = (uint16_t) h;
 #pragma unroll
             for (int i = 0; i != 16; ++i) m[i] = n[i];
+#endif
         }
     }
+#ifdef __CUDACC__
+    int min_element = 0, min_cost = (int) (m[0] & 0xFFFFu);
+#pragma unroll
+    for (int i = 0; i != 16; ++i) {
+        const int v = (int) ((m[i >> 1] >> (16 * (i & 1))) & 0xFFFFu);
+        if (v < min_cost) { min_cost = v; min_element = i; }
+    }
+#else
     int min_element = 0, min_cost = m[0];
 #pragma unroll
     for (int i = 0; i != 16; ++i)
         if (m[i] < min_cost) { min_cost = m[i]; min_element = i; }
+#endif
     uint32_t cost = (uint32_t) (long long) roundf((float) min_cost / 7.0f);
 
     const int n_bytes = (n_out + 7) / 8;
