@@ -90,6 +90,26 @@ def test_records_bit_exact_all_traffic_kinds(mode):
     assert sum(c.frames) == sum(len(r) for r in want)
 
 
+def test_weak_signal_high_cost_frames_bit_exact():
+    """Frames decoded from signals at -6 .. 3 dB SNR: Viterbi costs in the hundreds, many equal-metric
+    decisions, Golay words beyond repair, failed LSF CRCs -- the decoder's packed 16-bit path metrics must
+    give the reference's int32 results (payload, cost, type) bit for bit."""
+    rng = np.random.default_rng(77)
+    ps = [gen.default_params(seed=int(rng.integers(1, 1 << 40)), mode=gen.MIXED, snr_db=float(rng.uniform(-6, 3)),
+                             skew_ppm=float(rng.uniform(-200, 200)), repeat=1, gap=int(rng.integers(2000, 6000)),
+                             lead_in=int(rng.integers(0, 4800)), n_frames=int(rng.integers(4, 30)))
+          for _ in range(128)]
+    x = gen.generate(ps, 96000)
+    want, _ = ol.demod_batch("port", x)
+    with m.Demodulator(128, 9600, flags=m.STREAMING) as d:
+        got = d.demodulate(x, chunk=9600)
+        c = d.counters()
+    assert_records_match(want, got, "weak signal")
+    costs = np.concatenate([r["viterbi_cost"] for r in want if len(r)])
+    assert len(costs) > 300 and int(costs.max()) > 60
+    assert c.faults == 0 and c.dropped == 0
+
+
 def test_chunking_does_not_change_results():
     """Ragged submit sizes (not multiples of 8, 1 sample, larger than a frame) give identical records."""
     x = gen.generate(random_params(5, gen.MIXED, 33), 60011)
