@@ -1338,7 +1338,7 @@ M17B_FN int load_pair(const int16_t* p)
 #ifdef __CUDACC__
     // volatile: ptxas otherwise sinks each load to just before its use (register pressure), which exposes
     // a full L2 latency in front of every add-compare-select step (45 % of decode_kernel's stall samples,
-    // profiles/r01z); in program order all loads of a block are in flight together
+    // before r02e, see profiles/README.md); in program order all loads of a block are in flight together
     int v;
     asm volatile("ld.global.s16 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
