@@ -44,7 +44,9 @@ extern "C" {
 #define M17B_ENODEV   -2   /* no usable CUDA device / driver                       */
 #define M17B_ENOMEM   -3   /* device or host allocation failed                     */
 #define M17B_ECUDA    -4   /* a CUDA call or kernel failed (m17b_last_cuda_error)  */
-#define M17B_EOVERFLOW -5  /* frame record ring overflowed: drain more often       */
+#define M17B_EOVERFLOW -5  /* frame record ring overflowed: records were lost (counter `dropped`); returned once
+                              per loss, the surviving records stay drainable: drain more often / raise
+                              frame_capacity                                       */
 #define M17B_ESTATE   -6   /* internal invariant violated (counter `faults`)       */
 
 /* m17b_config.flags */
@@ -59,6 +61,9 @@ extern "C" {
                                 * always walks whole frames.  Every frame that ends inside a submit is still
                                 * delivered with that submit; m17b_sync / m17b_drain bring all streams up to
                                 * the newest sample first (their diagnostics then match the reference's).  */
+
+#define M17B_DIAG_RECORDS 0x10u /* record one m17b_diag_rec per reference diagnostic callback (m17b_diag_drain);
+                                 * for few-channel callers such as the CLI: 56 bytes per 384 / 960 samples and stream */
 
 /* m17b_submit location */
 #define M17B_HOST    0         /* samples points to host memory (pinned for full overlap)      */
@@ -79,7 +84,8 @@ typedef struct m17b_config {
     uint32_t flags;            /* M17B_FIR_FMA | M17B_INVERT | M17B_PROFILE                */
     uint32_t frame_capacity;   /* frame records buffered on the device between drains
                                   (0: n_streams * 2 * (max_chunk / 1600 + 2), the worst case)  */
-    uint32_t reserved[3];
+    uint32_t reserved[3];      /* zero.  reserved[0] is a test hook: ring position of every stream's first sample
+                                  (32-bit ring positions wrap after 2^32 samples per stream; tests start near the wrap) */
 } m17b_config;
 
 /*
@@ -115,6 +121,17 @@ typedef struct m17b_diag {
     int32_t  viterbi_cost;
     uint64_t samples;          /* samples of this stream processed so far                  */
 } m17b_diag;
+
+/* One record per invocation the reference would have made of diagnostic_callback_t: every 384 samples
+ * while the carrier detect is off (evm argument = dev.error() = 0, M17Demodulator.h:675-689,
+ * FreqDevEstimator.h:53) and every 960 samples while it is on (:742-752).  d.samples = samples of the
+ * stream processed when it fires (the callback runs after the frame callback of the same sample).
+ * Recorded only by contexts created with M17B_DIAG_RECORDS. */
+typedef struct m17b_diag_rec {
+    uint32_t  stream;
+    uint32_t  pad;
+    m17b_diag d;
+} m17b_diag_rec;               /* 56 bytes */
 
 typedef struct m17b_counters {
     uint64_t samples;          /* samples demodulated over all streams                     */
@@ -184,6 +201,9 @@ int  m17b_drain_upto(m17b_ctx* ctx, unsigned long long ticket, m17b_frame* out, 
 int  m17b_pending_frames(m17b_ctx* ctx, size_t* n);
 
 int  m17b_diag_get(m17b_ctx* ctx, uint32_t stream, m17b_diag* out);
+/* m17b_sync(), then move up to `cap` diagnostic records (M17B_DIAG_RECORDS contexts only) to `out`, per stream in
+ * chronological order; call again while *n == cap. */
+int  m17b_diag_drain(m17b_ctx* ctx, m17b_diag_rec* out, size_t cap, size_t* n);
 int  m17b_counters_get(m17b_ctx* ctx, m17b_counters* out);
 int  m17b_get_profile(m17b_ctx* ctx, m17b_profile* out, int reset);
 
@@ -197,6 +217,12 @@ int  m17b_event_elapsed(m17b_ctx* ctx, int a, int b, double* ms);
  * in the filter mode the context was created with. */
 int  m17b_debug_filter(m17b_ctx* ctx, const int16_t* samples_host, size_t n, size_t stream_stride,
                        float* filtered_host /* [n_streams][n] */, float* scaled_host /* may be NULL */);
+
+/* ... and Correlator::sample + correlate (Correlator.h:43-64) clocked on every one of those filter outputs from a
+ * fresh correlator: per sample {limit_, correlation with the preamble, LSF/stream, packet/BERT, EOT sync word}
+ * (M17Demodulator.h:154-157), computed by the arithmetic the sync-word search pass uses. */
+int  m17b_debug_correlate(m17b_ctx* ctx, const int16_t* samples_host, size_t n, size_t stream_stride,
+                          float* filtered_host /* [n_streams][n] */, float* corr_host /* [n_streams][n][5] */);
 
 /* FP32 pipe microbenchmark: sustained FFMA throughput of the context's GPU in TFLOP/s
  * (2 flop per FMA), the denominator of the matched filter's roofline fraction.

@@ -63,6 +63,8 @@ struct m17b_ctx {
     unsigned long long ticket = 0;             // submits issued
     unsigned long long slot_ticket[kSlots] = {};
     uint32_t rec_read = 0;                     // record cursor consumed by the host (monotonic, mod 2^32)
+    unsigned long long dropped_reported = 0;   // overflow already signalled to the caller (M17B_EOVERFLOW is returned once per loss)
+    uint32_t diag_read = 0;                    // diagnostic-record cursor consumed by the host
 };
 
 namespace {
@@ -190,7 +192,8 @@ void free_all(m17b_ctx* c)
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
     for (auto& e : c->done) if (e) cudaEventDestroy(e);
     if (c->snap) cudaFreeHost(c->snap);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.corr_ring); cudaFree(c->d.lim_save); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.mask_ring); cudaFree(c->d.ckpt_ring);
+    cudaFree(c->d.corr_snap); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list); cudaFree(c->d.diag_recs);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -240,6 +243,7 @@ int m17b_device_count(void)
 int m17b_create(const m17b_config* cfg, m17b_ctx** out)
 {
     if (!cfg || !out || cfg->n_streams == 0 || cfg->max_chunk == 0) return M17B_EINVAL;
+    if (cfg->reserved[0] % 32u != 0 || cfg->reserved[1] || cfg->reserved[2]) return M17B_EINVAL;
     *out = nullptr;
     int ndev = m17b_device_count();
     if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return M17B_ENODEV;
@@ -274,9 +278,11 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         // running their rounds (front stream), so a lane may be a whole chunk further behind the newest ring write
         uint32_t need = cfg->max_chunk * ((cfg->flags & M17B_STREAMING) ? 2u : 1u) + kRoundCap + 160 + 16;
         d.ring_lines = next_pow2((need + kLine - 1) / kLine + 1);
-        // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart
+        // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart; room for
+        // three submits: the one being drained and two enqueued behind it (m17b_drain_upto pipelines of depth <= 2;
+        // deeper pipelines pass their own frame_capacity)
         d.rec_cap = cfg->frame_capacity ? cfg->frame_capacity
-                                        : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 2 * (cfg->max_chunk / kMinFrameSpacing + 2), 0x7fffffffull);
+                                        : (uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 6 * (cfg->max_chunk / kMinFrameSpacing + 2), 0x7fffffffull);
         d.rec_cap = next_pow2(std::max(d.rec_cap, 64u));          // slot = cursor % rec_cap must survive cursor wrap-around
         d.rec_read = 0;
         for (auto& e : c->done) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -288,8 +294,14 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.ring_y, ring_bytes));
         CK(cudaMalloc(&d.ring_d, ring_bytes));
         CK(cudaMalloc(&d.ring_x, ring_bytes / 2));
-        CK(cudaMalloc(&d.corr_ring, 96 * np * sizeof(float)));
-        CK(cudaMalloc(&d.lim_save, 8 * np * sizeof(float)));
+        CK(cudaMalloc(&d.mask_ring, (size_t) d.ring_lines * np * 4 * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.ckpt_ring, (size_t) d.ring_lines * np * 4 * sizeof(float2)));
+        CK(cudaMalloc(&d.corr_snap, 80 * np * sizeof(float)));
+        if (cfg->flags & M17B_DIAG_RECORDS) {
+            // one record per 384 samples and stream at most; room for three submits like the frame records
+            d.diag_cap = next_pow2((uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 3 * (cfg->max_chunk / 384 + 2), 0x40000000ull));
+            CK(cudaMalloc(&d.diag_recs, (size_t) d.diag_cap * sizeof(m17b_diag_rec)));
+        }
         // a scan lane may lag the head by the ring span; its window starts up to 960 samples earlier, and the
         // first window's entry must survive 1920 samples longer
         d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
@@ -306,8 +318,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMemsetAsync(d.ring_y, 0, ring_bytes, c->compute));
         CK(cudaMemsetAsync(d.ring_d, 0, ring_bytes, c->compute));
         CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes / 2, c->compute));
-        CK(cudaMemsetAsync(d.corr_ring, 0, 96 * np * sizeof(float), c->compute));
-        CK(cudaMemsetAsync(d.lim_save, 0, 8 * np * sizeof(float), c->compute));
+        CK(cudaMemsetAsync(d.mask_ring, 0, (size_t) d.ring_lines * np * 4 * sizeof(uint32_t), c->compute));
+        CK(cudaMemsetAsync(d.ckpt_ring, 0, (size_t) d.ring_lines * np * 4 * sizeof(float2), c->compute));
+        CK(cudaMemsetAsync(d.corr_snap, 0, 80 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.sw_samples, 0, 30 * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.fir_snap, 0, (size_t) kTapsUsed * np * sizeof(float), c->compute));
         CK(cudaMemsetAsync(d.llr, 0, 184 * np * sizeof(int16_t), c->compute));
@@ -324,7 +337,10 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         build_tables(tab, golay.data());
         CK(upload_tables(tab, golay.data()));
         CK(configure_kernels());
-        launch_init_state(d, c->compute);
+        // debug hook (tests): the stream's first sample sits at ring position `origin` instead of 0, so that a
+        // short run crosses the 2^32 wrap of the 32-bit ring positions
+        c->head = cfg->reserved[0];
+        launch_init_state(d, c->head, c->compute);
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(c->compute));
         return M17B_OK;
@@ -470,7 +486,10 @@ int m17b_sync(m17b_ctx* c)
         if ((rc = fetch_counters(c)) != M17B_OK) return rc;
     }
     ev_collect(c);
-    if (c->host_ctr.dropped) return M17B_EOVERFLOW;
+    if (c->host_ctr.dropped != c->dropped_reported) {       // signalled once per loss; the surviving records stay drainable
+        c->dropped_reported = c->host_ctr.dropped;
+        return M17B_EOVERFLOW;
+    }
     return M17B_OK;
 }
 
@@ -505,6 +524,7 @@ int m17b_drain_upto(m17b_ctx* c, unsigned long long ticket, m17b_frame* out, siz
 {
     if (!c || !n || (!out && cap)) return M17B_EINVAL;
     *n = 0;
+    bool overflow = false;
     CK(cudaSetDevice(c->cfg.device));
     if (c->ready_off == c->ready_n && ticket != 0) {
         if (ticket > c->ticket) return M17B_EINVAL;
@@ -514,16 +534,36 @@ int m17b_drain_upto(m17b_ctx* c, unsigned long long ticket, m17b_frame* out, siz
         const int slot = (int) ((t - 1) % m17b_ctx::kSlots);
         CK(cudaEventSynchronize(c->done[slot]));
         const Counters& k = c->snap[slot];
-        if (k.dropped) return M17B_EOVERFLOW;
         int rc = pull_records(c, k.rec_count);
         if (rc != M17B_OK) return rc;
+        if (k.dropped != c->dropped_reported) { c->dropped_reported = k.dropped; overflow = true; }
     }
     size_t k = std::min(cap, c->ready_n - c->ready_off);
     if (k) std::memcpy(out, c->ready + c->ready_off, k * sizeof(m17b_frame));
     c->ready_off += k;
     *n = k;
     c->prof.decode_frames += k;
-    return M17B_OK;
+    return overflow ? M17B_EOVERFLOW : M17B_OK;
+}
+
+int m17b_diag_drain(m17b_ctx* c, m17b_diag_rec* out, size_t cap, size_t* n)
+{
+    if (!c || !n || (!out && cap)) return M17B_EINVAL;
+    *n = 0;
+    if (!c->d.diag_recs) return M17B_EINVAL;                // context created without M17B_DIAG_RECORDS
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    uint32_t avail = c->host_ctr.diag_count - c->diag_read;
+    if (avail > c->d.diag_cap) { c->diag_read = c->host_ctr.diag_count - c->d.diag_cap; avail = c->d.diag_cap; }
+    const uint32_t k = (uint32_t) std::min<size_t>(cap, avail);
+    const uint32_t first = c->diag_read & (c->d.diag_cap - 1);
+    const uint32_t n1 = std::min(k, c->d.diag_cap - first);
+    if (n1) CK(cudaMemcpy(out, c->d.diag_recs + first, sizeof(m17b_diag_rec) * n1, cudaMemcpyDeviceToHost));
+    if (k != n1) CK(cudaMemcpy(out + n1, c->d.diag_recs, sizeof(m17b_diag_rec) * (k - n1), cudaMemcpyDeviceToHost));
+    c->diag_read += k;
+    c->d.diag_read = c->diag_read;
+    *n = k;
+    return c->host_ctr.diag_dropped ? M17B_EOVERFLOW : M17B_OK;
 }
 
 int m17b_diag_get(m17b_ctx* c, uint32_t stream, m17b_diag* out)
@@ -538,7 +578,9 @@ int m17b_diag_get(m17b_ctx* c, uint32_t stream, m17b_diag* out)
     uint32_t fl = f[F_FLAGS];
     // arguments of diagnostic_callback at M17Demodulator.h:746-750
     out->dcd = (fl & FL_DCD) ? 1 : 0;
-    out->evm = std::sqrt(asf(F_EVM));                                     // SymbolEvm::evm(), StandardDeviation.h:79-82
+    // the evm argument is SymbolEvm::evm() (StandardDeviation.h:79-82) at the update points reached with the carrier
+    // detect on (:746) and dev.error() == 0 (FreqDevEstimator.h:53) at those reached with it off (:683)
+    out->evm = (fl & FL_DCD) ? std::sqrt(asf(F_EVM)) : 0.f;
     out->deviation = 2400.f / asf(F_IDEV);                                // FreqDevEstimator.h:52
     out->offset = asf(F_OFFSET);
     out->locked = ((fl >> FL_STATE_SHIFT) & 7) != ST_UNLOCKED;
@@ -595,8 +637,8 @@ int m17b_event_elapsed(m17b_ctx* c, int a, int b, double* ms)
     return M17B_OK;
 }
 
-int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t stride, float* filtered_host,
-                      float* scaled_host)
+static int debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t stride, float* filtered_host,
+                        float* scaled_host, float* corr_host)
 {
     if (!c || !samples_host || !filtered_host || n == 0 || stride < n) return M17B_EINVAL;
     CK(cudaSetDevice(c->cfg.device));
@@ -607,7 +649,7 @@ int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t
     t.ring_lines = next_pow2((uint32_t) ((n + kLine - 1) / kLine + 1));
     size_t ring_bytes = (size_t) t.ring_lines * t.np * kLine * sizeof(float);
     int16_t *din = nullptr, *dtail = nullptr;
-    float *dy = nullptr, *dx = nullptr;
+    float *dy = nullptr, *dx = nullptr, *dcorr = nullptr;
     int rc = [&]() -> int {
         CK(cudaMalloc(&t.ring_y, ring_bytes));
         CK(cudaMalloc(&t.ring_d, ring_bytes));
@@ -620,6 +662,11 @@ int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t
         CK(cudaMemcpy2DAsync(din, n * sizeof(int16_t), samples_host, stride * sizeof(int16_t), n * sizeof(int16_t), ns,
                              cudaMemcpyHostToDevice, c->compute));
         launch_fir(t, din, n, (uint32_t) n, dtail, 0, c->cfg.flags & M17B_FIR_FMA, c->cfg.flags & M17B_INVERT, c->compute);
+        if (corr_host) {
+            CK(cudaMalloc(&dcorr, (size_t) ns * n * 5 * sizeof(float)));
+            launch_debug_corr(t, (uint32_t) n, dcorr, c->compute);
+            CK(cudaMemcpyAsync(corr_host, dcorr, (size_t) ns * n * 5 * sizeof(float), cudaMemcpyDeviceToHost, c->compute));
+        }
         launch_gather(t, (uint32_t) n, dy, dx, c->compute);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(filtered_host, dy, (size_t) ns * n * sizeof(float), cudaMemcpyDeviceToHost, c->compute));
@@ -628,8 +675,21 @@ int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t
         CK(cudaStreamSynchronize(c->compute));
         return M17B_OK;
     }();
-    cudaFree(t.ring_y); cudaFree(t.ring_d); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx);
+    cudaFree(t.ring_y); cudaFree(t.ring_d); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx); cudaFree(dcorr);
     return rc;
+}
+
+int m17b_debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t stride, float* filtered_host,
+                      float* scaled_host)
+{
+    return debug_filter(c, samples_host, n, stride, filtered_host, scaled_host, nullptr);
+}
+
+int m17b_debug_correlate(m17b_ctx* c, const int16_t* samples_host, size_t n, size_t stride, float* filtered_host,
+                         float* corr_host)
+{
+    if (!corr_host) return M17B_EINVAL;
+    return debug_filter(c, samples_host, n, stride, filtered_host, nullptr, corr_host);
 }
 
 int m17b_measure_fp32_peak(m17b_ctx* c, int variant, double* tflops)

@@ -18,8 +18,13 @@
 //       rare paths that rebuild filter history after a carrier-detect gap.
 //   per-stream scalars            : uint32 [Np/32][NFIELDS][32]   (one coalesced
 //       128 B line per field per warp)
-//   correlator ring               : float [96][Np]    (Correlator::buffer_ + one block of look-ahead)
-//   limit look-ahead              : float [8][Np]     (limit_ of samples the dense pass ran ahead by)
+//   sync-word trigger masks       : uint32 [RL][Np][4]   one word per 8-sample block: bit 8w + j set when sync word w
+//                                   (0 preamble, 1 LSF/stream, 2 packet/BERT) triggers on block sample j
+//                                   (Correlator.h:150-157); written by fixup_kernel's search pass for the span a
+//                                   searching stream (ST_UNLOCKED, carrier detect on) has ahead of it
+//   limit-filter checkpoints      : float2 [RL][Np][4]   history of Correlator::sample_filter after every block
+//                                   of a searched span (the stream adopts it where it leaves the search)
+//   correlator snapshot           : float [80][Np]    (Correlator::buffer_ frozen when the carrier detect gates it)
 //   carrier-detect window sums    : float [n_seg][4][Np]  (dcd_kernel: energy sums of both sliding-DFT bins
 //                                   384 and 960 samples after every 192-aligned window start)
 //   sync-word peak samples        : float [30][Np]    (SyncWord::samples_ x3)
@@ -41,7 +46,7 @@ constexpr int kTailLen = 160;         // raw history kept between submits (>= 14
 constexpr int kChunk = 8;             // samples per scan block (one 32-byte sector)
 constexpr int kLine = 32;             // samples per ring line (128 bytes of float)
 constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:149: 48000/400)
-constexpr int kRoundCap = 2048;       // samples a stream may advance per scan launch
+constexpr int kRoundCap = 2048;       // ring slack: samples a stream may trail the head by beyond one submit
 constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
 constexpr int kSeg = 192;             // gcd of the carrier-detect cadences 384 / 960 and of the 1920-sample start-up
 constexpr int kFirstUpdate = 1920 + 384;   // position of a stream's first carrier-detect update (M17Demodulator.h:659-689)
@@ -49,7 +54,8 @@ constexpr int kFirstUpdate = 1920 + 384;   // position of a stream's first carri
 enum Field : int {
     F_POS = 0,
     F_RE0, F_IM0, F_RE1, F_IM1, F_L1, F_L2, F_LEVEL,
-    F_IIR0, F_IIR1, F_LIMIT,
+    F_IIR0, F_IIR1, // limit biquad history (Correlator.h:38-41) at F_POS; frozen while the carrier detect gates it
+    F_SFROM, F_STO, // span [from, to) the search pass has covered for this stream's current search
     F_CNT,          // count_ (low 16) | initializing (high 16)
     F_IDX,          // corr_pos (8) | framer_index (16) << 8 | gap_k (8) << 24
     F_FLAGS,
@@ -62,8 +68,6 @@ enum Field : int {
     F_IDEV, F_OFFSET, F_EVM,
     F_DEC,          // dec_state (8) | lich_segments (8) << 8 | depunct401 (8) << 16
     F_SEQ,
-    F_DPOS,         // position of the dense pass (>= F_POS, same 8-sample block)
-    F_RP,           // next physical slot of the 96-entry correlator ring
     F_GAPR,         // position at which the matched filter last resumed after a carrier-detect gap
     F_GAPDONE,      // outputs after F_GAPR already corrected by fixup_kernel (0..149)
     F_ACC1,         // dcd_kernel: five rolling carrier-detect energy sums of bin 0 (window phases), F_ACC1 + i
@@ -84,7 +88,7 @@ constexpr uint32_t FL_NEED_UPDATE = 1u << 20;
 constexpr uint32_t FL_DEV_RESET = 1u << 21;
 constexpr uint32_t FL_EOT = 1u << 22;
 constexpr uint32_t FL_PENDING = 1u << 23;     // a frame is complete: decode_kernel's turn
-constexpr uint32_t FL_FIXUP = 1u << 24;       // filter outputs after a gap are due: fixup_kernel's turn
+constexpr uint32_t FL_FIXUP = 1u << 24;       // filter outputs after a gap and / or a sync-word search are due: fixup_kernel's turn
 
 enum DemodState : int { ST_UNLOCKED, ST_LSF_SYNC, ST_STREAM_SYNC, ST_PACKET_SYNC, ST_BERT_SYNC, ST_SYNC_WAIT, ST_FRAME, ST_TBD };
 enum DecState : int { DEC_LSF, DEC_STREAM, DEC_BASIC_PACKET, DEC_FULL_PACKET, DEC_BERT };
@@ -101,6 +105,9 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
     unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
     unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
+    unsigned int diag_count;      // diagnostic-record cursor (M17B_DIAG_RECORDS), monotonic like rec_count
+    unsigned int pad0;
+    unsigned long long diag_dropped;
 };
 
 struct DevPtrs {
@@ -108,9 +115,10 @@ struct DevPtrs {
     float* ring_y;                // [RL][Np][32]
     float* ring_d;                // [RL][Np][32]
     int16_t* ring_x;              // [RL][Np][32]
-    float* corr_ring;             // [96][Np]
-    float* lim_save;              // [8][Np]
+    uint32_t* mask_ring;          // [RL][Np][4] sync-word trigger masks, one word per 8-sample block
+    float* corr_snap;             // [80][Np] the correlator's last 80 samples before a carrier-detect gap
     float* seg_ring;              // [n_seg][4][Np] carrier-detect energy sums per window start (see dcd_lane)
+    float2* ckpt_ring;            // [RL][Np][4] limit-filter history after every 8-sample block of a searched span
     uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
     uint32_t* dec_list;           // [5][Np] streams with a completed frame, by decode kind (0..3 = Viterbi map, 4 = LICH / none)
     float* sw_samples;            // [30][Np]
@@ -118,6 +126,7 @@ struct DevPtrs {
     int16_t* llr;                 // [184][Np]
     uint8_t* dec_bytes;           // [56][Np]
     m17b_frame* recs;             // [rec_cap]
+    m17b_diag_rec* diag_recs;     // [diag_cap] or null: diagnostics at the reference's update points (M17B_DIAG_RECORDS)
     Counters* ctr;
     uint32_t n_streams;
     uint32_t np;                  // padded stream count (multiple of 128)
@@ -125,6 +134,8 @@ struct DevPtrs {
     uint32_t n_seg;               // entries of seg_ring, power of two, n_seg * 192 > ring span + 960
     uint32_t rec_cap;             // power of two
     uint32_t rec_read;            // cursor up to which the host has taken the records (at launch time)
+    uint32_t diag_cap;            // power of two
+    uint32_t diag_read;
 };
 
 __host__ __device__ inline size_t st_index(uint32_t s, int f)
@@ -164,7 +175,8 @@ void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, boo
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);
-void launch_init_state(const DevPtrs& d, cudaStream_t s);
+void launch_init_state(const DevPtrs& d, uint32_t origin, cudaStream_t s);
+void launch_debug_corr(const DevPtrs& d, uint32_t n, float* out, cudaStream_t s);
 cudaError_t configure_kernels();
 double run_fp32_peak(int variant, int sm_count, cudaStream_t s);
 

@@ -3,11 +3,17 @@
 //   fir_kernel     (A) int16 -> float scaling (apps/m17-demod.cpp:489) + 150-tap RRC
 //                      matched filter (FirFilter.h:28-43, taps M17Demodulator.h:79-118)
 //                      for every stream and every new sample; FP32 pipe.
+//   dcd_kernel     (A2) the carrier detect's two-bin sliding DFT (SlidingDFT.h:118-132),
+//                      all streams in lock-step over a submit's new samples.
 //   scan_kernel    (B) per-stream serial part of M17Demodulator::operator()
-//                      (M17Demodulator.h:656-753): sliding-DFT carrier detect, limit
-//                      biquad, sync-word correlators, Kalman clock recovery, deviation /
-//                      offset estimator, 4-FSK soft slicer, framer.  One thread per
-//                      stream, every lane at its own stream position.
+//                      (M17Demodulator.h:656-753): limit biquad, carrier-detect cadence,
+//                      sync windows, Kalman clock recovery, deviation / offset estimator,
+//                      4-FSK soft slicer, framer.  One thread per stream, every lane at its
+//                      own stream position.
+//   fixup_kernel   (B2) what a stream asks for when it cannot go on alone: the matched
+//                      filter outputs after a carrier-detect gap (stale history), and the
+//                      sync-word search of ST_UNLOCKED (Correlator.h:43-64,146-157) over the
+//                      samples ahead of it, one thread per sample.
 //   decode_kernel  (C) M17FrameDecoder::operator() (M17FrameDecoder.h:353-392):
 //                      derandomise + deinterleave + depuncture folded into one index
 //                      map, soft Viterbi, Golay24 LICH, CRC16, decoder state machine,
@@ -30,35 +36,6 @@ namespace m17b {
 __constant__ ConstTables c_tab;
 __device__ uint32_t g_golay[2048];
 
-// Taps as compile-time literals so the fully unrolled filter loop carries them as
-// instruction immediates (FFMA/FMUL imm form).  Same values as ConstTables::taps.
-#define M17B_RRC_HALF \
-    0.0029364388513841593, 0.0031468394550958484, 0.002699564567597445, 0.001661182944400927, \
-    0.00023319405581230247, -0.0012851320781224025, -0.0025577136087664687, -0.0032843366522956313, \
-    -0.0032697038088887226, -0.0024733964729590865, -0.0010285696910973807, 0.0007766690889758685, \
-    0.002553421969211845, 0.0038920145144327816, 0.004451886520053017, 0.00404219185231544, \
-    0.002674727068399207, 0.0005756567993179152, -0.0018493784971116507, -0.004092346891623224, \
-    -0.005648131453822014, -0.006126925416243605, -0.005349511529163396, -0.003403189203405097, \
-    -0.0006430502751187517, 0.002365929161655135, 0.004957956568090113, 0.006506845894531803, \
-    0.006569574194782443, 0.0050017573119839134, 0.002017321931508163, -0.0018256054303579805, \
-    -0.00571615173291049, -0.008746639552588416, -0.010105075751866371, -0.009265784007800534, \
-    -0.006136551625729697, -0.001125978562075172, 0.004891777252042491, 0.01071805138282269, \
-    0.01505751553351295, 0.01679337935001369, 0.015256245142156299, 0.01042830577908502, \
-    0.003031522725559901, -0.0055333532968188165, -0.013403099825723372, -0.018598682349642525, \
-    -0.01944761739590459, -0.015005271935951746, -0.0053887880354343935, 0.008056525910253532, \
-    0.022816244158307273, 0.035513467692208076, 0.04244131815783876, 0.04025481153629372, \
-    0.02671818654865632, 0.0013810216516704976, -0.03394615682795165, -0.07502635967975885, \
-    -0.11540977897637611, -0.14703962203941534, -0.16119995609538576, -0.14969512896336504, \
-    -0.10610329539459686, -0.026921412469634916, 0.08757875030779196, 0.23293327870303457, \
-    0.4006012210123992, 0.5786324696325503, 0.7528286479934068, 0.908262741447522, \
-    1.0309661131633199, 1.1095611856548013, 1.1366197723675815
-
-__host__ __device__ constexpr float rrc_tap(int i)
-{
-    constexpr double half[75] = {M17B_RRC_HALF};
-    return i >= 149 ? 0.0f : float(i <= 74 ? half[i] : half[148 - i]);
-}
-
 cudaError_t upload_tables(const ConstTables& t, const uint32_t* golay)
 {
     cudaError_t e = cudaMemcpyToSymbol(c_tab, &t, sizeof(t));
@@ -73,7 +50,7 @@ cudaError_t upload_tables(const ConstTables& t, const uint32_t* golay)
 // float(double(s) / 41067.0) without double arithmetic: q = s*r, one Newton
 // correction with two FMAs gives the correctly rounded float quotient, which
 // equals the reference's double-rounded value for all 65536 inputs
-// (checked exhaustively in tests/test_scale.py and on the device in the GPU tests).
+// (tests/test_gpu_parity.py::test_scaling_all_int16_values_bit_exact).
 __device__ __forceinline__ float scale_sample(int v)
 {
     const float r = 0x1.988864p-16f;       // RN(1 / 41067)
@@ -308,8 +285,7 @@ void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_
 
 namespace m17b {
 
-constexpr int kScanThreads = RS;
-constexpr size_t kScanSmem = sizeof(float) * (kRing + 8) * kScanThreads + sizeof(LlrTable);
+constexpr int kScanThreads = 128;
 
 // Carrier-detect pre-pass (dcd_lane) over the new samples of a submit, all lanes
 // at the same position, two lanes (one per DFT bin) per stream.  Bound: FP32 issue; reads ring_d once (4 B/sample).
@@ -329,41 +305,21 @@ void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned lo
 __global__ void __launch_bounds__(kScanThreads)
 scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard)
 {
-    extern __shared__ float smem[];
-    float* ring_s = smem;                                  // [96][128] correlator rings
-    float* lim_s = smem + kRing * kScanThreads;            // [8][128] per-sample limits of the current block
-    LlrTable* tab = reinterpret_cast<LlrTable*>(smem + (kRing + 8) * kScanThreads);
+    __shared__ LlrTable tab;                               // lanes look up different entries: shared, not constant memory
     const int tid = threadIdx.x;
-    for (int i = tid; i < 48; i += kScanThreads) tab->thr[i] = llr_thr_padded(c_tab.llr_thr, i);
+    for (int i = tid; i < 48; i += kScanThreads) tab.thr[i] = llr_thr_padded(c_tab.llr_thr, i);
     for (int i = tid; i < 43; i += kScanThreads) {
-        tab->val[i] = (uint32_t) (uint8_t) c_tab.llr_val[i][0] | ((uint32_t) (uint8_t) c_tab.llr_val[i][1] << 8);
+        tab.val[i] = (uint32_t) (uint8_t) c_tab.llr_val[i][0] | ((uint32_t) (uint8_t) c_tab.llr_val[i][1] << 8);
     }
     __syncthreads();
-    const uint32_t s = blockIdx.x * kScanThreads + tid;      // < np: padded lanes stay in the warp as helpers
-
-    LaneIo e;
-    e.llr_tab = tab;
-    e.sb = d.st + st_index(s, 0);
-    e.ring = ring_s + tid;
-    e.lim = lim_s + tid;
-    e.ring_base = ring_s;
-    e.lim_base = lim_s;
-    e.col = tid;
-    e.sw_samples = d.sw_samples + s;
-    e.llr = d.llr + s;
-    e.snap = d.fir_snap + s;
-    e.ring_y = d.ring_y;
-    e.ring_d = d.ring_d;
-    e.ring_x = d.ring_x;
-    e.np = d.np;
-    e.lmask = d.ring_lines - 1;
-    e.s = s;
-    scan_lane(d, e, head, head64, s < d.n_streams, defer != 0, guard);
+    const uint32_t s = blockIdx.x * kScanThreads + tid;
+    if (s >= d.n_streams) return;
+    scan_lane(d, make_io(d, s, &tab), head, head64, true, defer != 0, guard);
 }
 
 void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s)
 {
-    scan_kernel<<<d.np / kScanThreads, kScanThreads, kScanSmem, s>>>(d, head, head64, defer ? 1 : 0, guard);
+    scan_kernel<<<d.np / kScanThreads, kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to
@@ -386,50 +342,123 @@ decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
     decode_lane(d, s, hist + threadIdx.x, head, head64);
 }
 
-// Matched-filter fix-up after a carrier-detect gap (M17Demodulator.h:675-689: the filter is not
-// clocked while !dcd_, so its first 149 outputs after it resumes see stale history; fir_kernel
-// computed them for contiguous history).  One CTA per waiting stream; thread k recomputes output
-// k in the reference's tap order from the snapshot and the scaled inputs staged in shared memory.
-constexpr int kFixThreads = 160;
+// What a stream asks for when it cannot go on alone (FL_FIXUP), one CTA per request:
+// (1) Matched-filter fix-up after a carrier-detect gap (M17Demodulator.h:675-689: the filter is not
+//     clocked while !dcd_, so its first 149 outputs after it resumes see stale history; fir_kernel
+//     computed them for contiguous history).  Thread k recomputes output k in the reference's tap order
+//     from the snapshot and the scaled inputs staged in shared memory.
+// (2) The sync-word search of a stream in ST_UNLOCKED with the carrier detect on (search_lane in
+//     m17b_lane.cuh is the serial statement of the same pass): do_unlocked() evaluates up to two
+//     correlations and their thresholds on EVERY sample (M17Demodulator.h:288-342).  That is feed-forward
+//     once limit_ is known, so per tile of 512 samples one thread runs the limit biquad (the only
+//     recurrence, ~12 dependent cycles per sample) and then every thread takes samples: three 8-tap
+//     correlations from the staged filter outputs and SyncWord::triggered's comparison.  The stream then
+//     jumps from trigger to trigger through the masks (scan_lane's search walk) and adopts the limit-filter
+//     history left at the block ends.
+constexpr int kFixThreads = 256;
+constexpr int kSearchTile = 512;
 
 __global__ void __launch_bounds__(kFixThreads)
 fixup_kernel(DevPtrs d, uint32_t head)
 {
     __shared__ float xs[kTapsUsed], snap[kTapsUsed];
+    __shared__ float ys[70 + kSearchTile];                 // filter outputs of [t0 - 70, t0 + tile) as the correlator saw them
+    __shared__ float lim[kSearchTile];                     // limit_ after each sample of the tile
+    __shared__ uint8_t tbits[kSearchTile];                 // trigger bits of each sample
     const uint32_t n_req = d.ctr->fix_count;
     const uint32_t cmask = d.ring_lines - 1;
     const int t = threadIdx.x;
     for (uint32_t q = blockIdx.x; q < n_req; q += gridDim.x) {
         const uint32_t s = d.fix_list[q];
         uint32_t* sb = d.st + st_index(s, 0);
+        // ---- (1) filter outputs after the resume position R ----
         const uint32_t R = sb[F_GAPR * 32];
         const int done = (int) sb[F_GAPDONE * 32];
         const uint32_t avail = head - R;
         const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
-        if (t < kTapsUsed) {
-            snap[t] = d.fir_snap[(size_t) t * d.np + s];
-            xs[t] = t < upto ? scale_i16(d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)]) : 0.f;
-        }
-        __syncthreads();
-        if (t >= done && t < upto) {
-            float result = 0.0f;
-            for (int i = 0; i != kTapsUsed; ++i) {
-                float v = i <= t ? xs[t - i] : snap[i - t - 1];
-                result = __fadd_rn(result, __fmul_rn(v, c_tab.taps[i]));
+        if (done < upto) {                                  // CTA-uniform
+            if (t < kTapsUsed) {
+                snap[t] = d.fir_snap[(size_t) t * d.np + s];
+                xs[t] = t < upto ? scale_i16(d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)]) : 0.f;
             }
-            d.ring_y[ring_off(R + (uint32_t) t, cmask, d.np, s)] = result;
+            __syncthreads();
+            if (t >= done && t < upto) {
+                float result = 0.0f;
+                for (int i = 0; i != kTapsUsed; ++i) {
+                    float v = i <= t ? xs[t - i] : snap[i - t - 1];
+                    result = __fadd_rn(result, __fmul_rn(v, c_tab.taps[i]));
+                }
+                d.ring_y[ring_off(R + (uint32_t) t, cmask, d.np, s)] = result;
+            }
+            __syncthreads();                                // the corrected outputs are read below
         }
-        __syncthreads();
+        // ---- (2) sync-word search over [F_POS, head) ----
+        if (wants_search(sb, head)) {                       // CTA-uniform
+            const uint32_t from = sb[F_POS * 32];
+            const int k0 = (int) (sb[F_IDX * 32] >> 24);    // samples clocked since the last resume, before `from`
+            const bool gap = k0 < kTapsUsed;                // ... which is then at Rk = from - k0; older samples are the snapshot's
+            const uint32_t Rk = from - (uint32_t) k0;
+            Biquad b;
+            b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
+            for (uint32_t t0 = from & ~7u; (int32_t) (head - t0) > 0; t0 += kSearchTile) {
+                const uint32_t left = head - t0;
+                const int n = left < (uint32_t) kSearchTile ? (int) left : kSearchTile;
+                for (int i = t; i < 70 + n; i += kFixThreads) {
+                    const uint32_t v = t0 - 70u + (uint32_t) i;
+                    float y;
+                    if (gap && (int32_t) (v - Rk) < 0) {
+                        const int idx = 79 - (int) (Rk - 1u - v);
+                        y = idx >= 0 ? d.corr_snap[(size_t) idx * d.np + s] : 0.f;     // idx < 0: never used (older than 70 before `from`)
+                    } else {
+                        y = d.ring_y[ring_off(v, cmask, d.np, s)];
+                    }
+                    ys[i] = y;
+                }
+                __syncthreads();
+                if (t == 0) {
+                    for (int i = 0; i != n; ++i) {
+                        const uint32_t p = t0 + (uint32_t) i;
+                        if ((int32_t) (p - from) < 0) continue;
+                        lim[i] = limit_step(b, ys[70 + i]);
+                        if ((p & 7u) == 7u) d.ckpt_ring[blk_off(p, cmask, d.np, s)] = make_float2(b.h1, b.h2);
+                    }
+                }
+                __syncthreads();
+                for (int i = t; i < kSearchTile; i += kFixThreads) {
+                    uint32_t bits = 0;
+                    if (i < n && (int32_t) (t0 + (uint32_t) i - from) >= 0) {
+                        float y8[8];
+#pragma unroll
+                        for (int j = 0; j != 8; ++j) y8[j] = ys[i + 10 * j];       // samples 70, 60, ..., 0 steps back
+                        bits = trigger_bits(lim[i], corr8(y8, kWordPreamble), corr8(y8, kWordLsf), corr8(y8, kWordPacket), 0.f);
+                    }
+                    tbits[i] = (uint8_t) bits;
+                }
+                __syncthreads();
+                if (t < (n + 7) / 8) {
+                    uint32_t word = 0;
+#pragma unroll
+                    for (int j = 0; j != 8; ++j) {
+                        const uint32_t bits = tbits[8 * t + j];
+                        word |= ((bits & 1u) << j) | (((bits >> 1) & 1u) << (8 + j)) | (((bits >> 2) & 1u) << (16 + j));
+                    }
+                    d.mask_ring[blk_off(t0 + 8u * (uint32_t) t, cmask, d.np, s)] = word;
+                }
+                __syncthreads();
+            }
+        }
         if (t == 0) {
-            sb[F_GAPDONE * 32] = (uint32_t) upto;
+            if (done < upto) sb[F_GAPDONE * 32] = (uint32_t) upto;
+            if (wants_search(sb, head)) { sb[F_SFROM * 32] = sb[F_POS * 32]; sb[F_STO * 32] = head; }
             sb[F_FLAGS * 32] &= ~FL_FIXUP;
         }
+        __syncthreads();
     }
 }
 
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
 {
-    fixup_kernel<<<sm_count * 4, kFixThreads, 0, s>>>(d, head);
+    fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head);
 }
 
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
@@ -441,9 +470,7 @@ void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, c
 // Per-device kernel attributes (dynamic shared memory above 48 KiB).
 cudaError_t configure_kernels()
 {
-    cudaError_t e = cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kScanSmem);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int) (sizeof(uint16_t) * 244 * kDecThreads));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(fir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -453,16 +480,44 @@ cudaError_t configure_kernels()
                                 (int) (sizeof(float) * kFirStreams * kFirRow));
 }
 
-__global__ void init_state_kernel(DevPtrs d)
+__global__ void init_state_kernel(DevPtrs d, uint32_t origin)
 {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= d.np) return;
-    init_lane(d.st + st_index(s, 0));
+    init_lane(d.st + st_index(s, 0), origin);
 }
 
-void launch_init_state(const DevPtrs& d, cudaStream_t s)
+void launch_init_state(const DevPtrs& d, uint32_t origin, cudaStream_t s)
 {
-    init_state_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d);
+    init_state_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, origin);
+}
+
+// m17b_debug_correlate: Correlator::sample + correlate (Correlator.h:43-64) clocked on every sample of a fresh
+// stream: limit_ and the correlations with the preamble, LSF / stream, packet / BERT and EOT sync words
+// (M17Demodulator.h:154-157) per sample, from the matched-filter outputs in `d`'s ring.  One thread per stream
+// (test-sized inputs); the arithmetic is limit_step / corr8, the very functions the search pass uses.
+__global__ void debug_corr_kernel(DevPtrs d, uint32_t n, float* __restrict__ out /* [n_streams][n][5] */)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= d.n_streams) return;
+    const uint32_t lmask = d.ring_lines - 1;
+    Biquad b; b.h1 = 0.f; b.h2 = 0.f;
+    for (uint32_t p = 0; p != n; ++p) {
+        float y8[8];
+#pragma unroll
+        for (int i = 0; i != 8; ++i) {
+            const int q = (int) p - 70 + 10 * i;
+            y8[i] = q >= 0 ? d.ring_y[ring_off((uint32_t) q, lmask, d.np, s)] : 0.f;      // Correlator::buffer_ starts zeroed
+        }
+        float* o = out + ((size_t) s * n + p) * 5;
+        o[0] = limit_step(b, y8[7]);
+        o[1] = corr8(y8, kWordPreamble); o[2] = corr8(y8, kWordLsf); o[3] = corr8(y8, kWordPacket); o[4] = corr8(y8, kWordEot);
+    }
+}
+
+void launch_debug_corr(const DevPtrs& d, uint32_t n, float* out, cudaStream_t s)
+{
+    debug_corr_kernel<<<(d.n_streams + 63) / 64, 64, 0, s>>>(d, n, out);
 }
 
 // ---------------------------------------------------------------------------

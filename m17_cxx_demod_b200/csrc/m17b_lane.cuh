@@ -1,4 +1,4 @@
-// m17b_lane.cuh -- the per-stream ("lane") logic of the scan and decode kernels.
+// m17b_lane.cuh -- the per-stream ("lane") logic of the scan, search and decode kernels.
 //
 // One lane = one M17 stream = one CUDA thread.  Everything here is straight-line
 // per-lane code with no warp intrinsics, so the very same source also compiles
@@ -7,29 +7,29 @@
 // the functions are __device__ only: the product has no CPU path.
 //
 //   scan_lane()    M17Demodulator::operator()                M17Demodulator.h:656-753
+//   search_lane()  the sync-word search of do_unlocked()     M17Demodulator.h:288-342, Correlator.h:43-64,146-157
 //   decode_lane()  M17FrameDecoder::operator()               M17FrameDecoder.h:353-392
 //
-// Structure of scan_lane (why it looks nothing like the reference's loop):
-// the reference does everything once per sample.  Only three things really are
-// per-sample recurrences: the two sliding-DFT bins of the carrier detect
-// (SlidingDFT.h:118-132), the correlator's limit biquad (Correlator.h:43-49) and
-// the correlator ring write.  The state machine around them acts on a few
-// samples per symbol at most.  A lane therefore walks its samples in aligned
-// blocks of 8 (one 32-byte sector of the sample ring) in two passes:
-//   dense pass   branch-free recurrences for the block's samples; the per-sample
-//                limit values go to a small shared-memory array;
-//   event pass   jumps from one sample the state machine can act on to the next
-//                (quiet_samples() gives the distance in closed form), running the
-//                reference's per-sample logic only there.
-// All lanes of a warp execute the dense pass together whatever state they are in;
-// the divergent part shrinks to the events.  The carrier-detect cadence (384 /
-// 960 samples) and the 1920-sample start-up are multiples of 8 from sample 0, so
-// mode changes (filter clocked or not) only ever happen at block ends.
-//
-// The dense pass may run ahead of the event pass inside one block (a lane stops
-// at the sample that completes a frame and waits for decode_kernel).  The
-// correlator ring therefore keeps 96 samples physically (the reference's 80 plus
-// a block of look-ahead) and is addressed relative to the sample being handled.
+// Structure of scan_lane (why it looks nothing like the reference's loop): the
+// reference does everything once per sample, but only the correlator's limit
+// biquad (Correlator.h:43-49) really is a per-sample recurrence of the clocked
+// path (the carrier detect's sliding DFT has its own lock-step pre-pass,
+// dcd_lane).  The state machine around it acts on a few samples per symbol at
+// most, and the correlator's 80-sample buffer is nothing but the last 80 filter
+// outputs, which the sample ring already holds.  A lane therefore walks aligned
+// blocks of 8 samples (one 32-byte sector of the sample ring): the limit filter
+// runs over the block in registers, and the reference's per-sample logic runs
+// only on the samples the state machine can act on (quiet_samples() gives the
+// distance in closed form); sync-word correlations are evaluated on demand, on
+// the few samples of a frame's sync window, straight from the sample ring.
+// The one state that evaluates correlations on EVERY sample -- ST_UNLOCKED with
+// the carrier detect on -- is feed-forward once the limit filter has run, so
+// it is not walked serially at all: the lane asks fixup_kernel for a search pass
+// over the samples ahead (one thread per sample) and then jumps from trigger to
+// trigger through the masks that pass leaves.
+// The carrier-detect cadence (384 / 960 samples) and the 1920-sample start-up
+// are multiples of 8 from sample 0, so mode changes (filter clocked or not)
+// only ever happen at block ends.
 #pragma once
 #include <cstddef>
 
@@ -53,7 +53,6 @@
 namespace m17b {
 
 #ifdef __CUDACC__
-constexpr int RS = 64;                // shared-memory column stride == threads per CTA
 M17B_FN float u2f(uint32_t v) { return __uint_as_float(v); }
 M17B_FN uint32_t f2u(float v) { return __float_as_uint(v); }
 M17B_FN float mul_rn(float a, float b) { return __fmul_rn(a, b); }
@@ -62,7 +61,6 @@ M17B_FN int popc(uint32_t v) { return __popc(v); }
 M17B_FN void ctr_add(unsigned long long* p, unsigned long long v) { atomicAdd(p, v); }
 M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { return atomicAdd(p, v); }
 #else
-constexpr int RS = 1;
 extern ConstTables h_tab;
 extern uint32_t h_golay[2048];
 M17B_FN float u2f(uint32_t v) { float f; memcpy(&f, &v, 4); return f; }
@@ -74,22 +72,9 @@ M17B_FN void ctr_add(unsigned long long* p, unsigned long long v) { *p += v; }
 M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { unsigned int o = *p; *p += v; return o; }
 #endif
 
-constexpr int kRing = 96;               // physical correlator ring (Correlator::buffer_ is 80)
-
-// Warp primitives.  The host build runs one lane at a time: a "warp" of one.
 #ifdef __CUDACC__
-M17B_FN bool warp_any(bool p) { return __any_sync(0xffffffffu, p); }
-M17B_FN uint32_t warp_ballot(bool p) { return __ballot_sync(0xffffffffu, p); }
-M17B_FN int warp_bcast(int v, int src) { return __shfl_sync(0xffffffffu, v, src); }
-M17B_FN void warp_sync() { __syncwarp(); }
-M17B_FN int lane_id() { return (int) (threadIdx.x & 31); }
 M17B_FN int first_set(uint32_t m) { return __ffs((int) m) - 1; }
 #else
-M17B_FN bool warp_any(bool p) { return p; }
-M17B_FN uint32_t warp_ballot(bool p) { return p ? 1u : 0u; }
-M17B_FN int warp_bcast(int v, int) { return v; }
-M17B_FN void warp_sync() {}
-M17B_FN int lane_id() { return 0; }
 M17B_FN int first_set(uint32_t m) { return __builtin_ffs((int) m) - 1; }
 #endif
 
@@ -190,26 +175,57 @@ M17B_FN int round_half_away(float v)
 }
 
 // ---------------------------------------------------------------------------
-// correlator ring access.  `ph` = physical slot of the sample being handled
-// (0..95); a sample clocked in d steps earlier sits at slot ph - d (mod 96).
+// Clocked-sample history.  The correlator's 80-sample buffer (Correlator.h:25-49)
+// is not materialised: its content is the last 80 matched-filter outputs the
+// demodulator CLOCKED, i.e. ring_y itself back to the position the filter last
+// resumed at after a carrier-detect gap, and before that the snapshot taken when
+// the gap began (corr_snap).
 // ---------------------------------------------------------------------------
 
-M17B_FN float ring_back(const float* ring, int ph, int d)
+struct LlrTable;
+
+struct LaneIo {
+    const LlrTable* llr_tab;
+    uint32_t* sb;          // &st[block][0][lane]
+    float* sw_samples;     // + s, stride np
+    int16_t* llr;          // + s, stride np
+    float* snap;           // + s, stride np: matched-filter history frozen by a carrier-detect gap
+    float* csnap;          // + s, stride np: correlator history frozen by a carrier-detect gap
+    const float* ring_y;
+    const int16_t* ring_x;
+    const uint32_t* mask_ring;
+    const float2* ckpt_ring;
+    uint32_t np, lmask, s;
+};
+
+M17B_FN size_t ring_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
 {
-    int p = ph - d;
-    p = p < 0 ? p + kRing : p;
-    return ring[p * RS];
+    return ((size_t) ((p >> 5) & lmask) * np + s) * kLine + (p & (kLine - 1));
+}
+
+// index of the 8-sample block that contains p in mask_ring / ckpt_ring ([RL][Np][4])
+M17B_FN size_t blk_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
+{
+    return ((size_t) ((p >> 5) & lmask) * np + s) * 4 + ((p >> 3) & 3u);
+}
+
+// y of the sample clocked d steps before the one at ring position p; k = samples clocked since the
+// correlator last resumed, counting the one at p (saturates at kTapsUsed: no gap within reach)
+M17B_FN float y_back(const LaneIo& e, uint32_t p, int k, int d)
+{
+    if (d < k) return e.ring_y[ring_off(p - (uint32_t) d, e.lmask, e.np, e.s)];
+    return e.csnap[(size_t) (79 - (d - k)) * e.np];
 }
 
 // Correlator.h:51-64: sum over i of sync[i] * buffer_[(prev_pos + 10 (i + 1)) % 80],
 // i.e. the samples 70, 60, ..., 0 steps back, oldest first.
-M17B_FN float correlate(const float* ring, int ph, uint32_t word /* bit i: sync[i] = -3 */)
+M17B_FN float correlate(const LaneIo& e, uint32_t p, int k, uint32_t word /* bit i: sync[i] = -3 */)
 {
     float result = 0.f;
 #pragma unroll
     for (int i = 0; i != 8; ++i) {
         float sy = ((word >> i) & 1) ? -3.f : 3.f;
-        result = result + sy * ring_back(ring, ph, 70 - 10 * i);
+        result = result + sy * y_back(e, p, k, 70 - 10 * i);
     }
     return result;
 }
@@ -221,22 +237,63 @@ constexpr uint32_t kWordPacket = 0xF2;     // +3,-3,+3,+3,-3,-3,-3,-3
 constexpr uint32_t kWordEot = 0x40;        // +3,+3,+3,+3,+3,+3,-3,+3
 constexpr float kLowest = -3.402823466e+38f;   // numeric_limits<float>::lowest(), Correlator.h:143
 
+// Correlator::sample's limit filter: BaseIirFilter<float,3> (IirFilter.h:26-42) with the coefficients of
+// Correlator.h:38-39 on |filtered sample|.  h1 / h2 = the filter's history, newest first.
+struct Biquad { float h1, h2; };
+
+M17B_FN float limit_step(Biquad& b, float y)
+{
+    float h0 = fabsf(y);
+    h0 -= -1.98148851f * b.h1;
+    h0 -= 0.98165828f * b.h2;
+    float r = 0.f;
+    r += 4.24433681e-05f * h0;
+    r += 8.48867363e-05f * b.h1;
+    r += 4.24433681e-05f * b.h2;
+    b.h2 = b.h1; b.h1 = h0;
+    return r;
+}
+
+// SyncWord::triggered (Correlator.h:150-157) reduced to its decision, for the sync words of
+// M17Demodulator.h:154-157: bit w of the result <=> triggered() returns non-zero for word w
+// (0 preamble, 1 LSF / stream, 2 packet / BERT, 3 EOT) given limit_ and the four correlations.
+M17B_FN uint32_t trigger_bits(float limit, float vp, float vl, float vk, float ve)
+{
+    const float l29 = limit * 29.f, l31 = limit * 31.f, lm31 = limit * -31.f, llow = limit * kLowest;
+    uint32_t b = 0;
+    b |= ((vp > l29 || vp < llow) && vp != 0.f) ? 1u : 0u;
+    b |= ((vl > l31 || vl < lm31) && vl != 0.f) ? 2u : 0u;
+    b |= ((vk > l31 || vk < lm31) && vk != 0.f) ? 4u : 0u;
+    b |= ((ve > l31 || ve < llow) && ve != 0.f) ? 8u : 0u;
+    return b;
+}
+
+// the correlation of Correlator.h:51-64 from the eight samples 70, 60, ..., 0 steps back (oldest first)
+M17B_FN float corr8(const float (&y8)[8], uint32_t word)
+{
+    float result = 0.f;
+#pragma unroll
+    for (int i = 0; i != 8; ++i) {
+        float sy = ((word >> i) & 1) ? -3.f : 3.f;
+        result = result + sy * y8[i];
+    }
+    return result;
+}
+
 // Correlator.h:150-157
-M17B_FN float sync_triggered(const float* ring, int ph, float limit, uint32_t word, float m1, float m2)
+M17B_FN float sync_triggered(const LaneIo& e, uint32_t p, int k, float limit, uint32_t word, float m1, float m2)
 {
     float limit_1 = limit * m1;
     float limit_2 = limit * m2;
-    float value = correlate(ring, ph, word);
+    float value = correlate(e, p, k, word);
     return (value > limit_1 || value < limit_2) ? value : 0.0f;
 }
 
-// Correlator.h:161-207: SyncWord::operator() followed by updated().  `f` is the
-// packed {timing_index:4, triggered:1}; returns new f | (updated & 3) << 8
+// Correlator.h:161-207: SyncWord::operator() followed by updated(), given triggered()'s value.  `f` is
+// the packed {timing_index:4, triggered:1}; returns new f | (updated & 3) << 8
 // (updated: 0, 1, or 3 for -1).  samples = SyncWord::samples_ column, stride np.
-M17B_FN_COLD uint32_t sync_step(float* samples, size_t np, const float* ring, int ph, int idx10, float limit,
-                                uint32_t word, float m1, float m2, uint32_t f)
+M17B_FN_COLD uint32_t sync_step(float* samples, size_t np, float value, int idx10, uint32_t f)
 {
-    float value = sync_triggered(ring, ph, limit, word, m1, m2);
     uint32_t timing_index = f & 0xF;
     bool trig = (f >> 4) & 1;
     uint32_t updated = 0;
@@ -261,11 +318,11 @@ M17B_FN_COLD uint32_t sync_step(float* samples, size_t np, const float* ring, in
 
 // M17Demodulator.h:232-241: Correlator::outer_symbol_levels (Correlator.h:81-114,
 // incl. `avg = max + min / 2.`) + FreqDevEstimator::update (FreqDevEstimator.h:31-48).
-// pp = logical buffer position (0..79) of the sample being handled, ph its physical
-// slot.  Returns (offset, idev); dev.reset_ is always false afterwards.
+// pp = logical buffer position (0..79) of the sample being handled, p its ring position, k the
+// samples clocked since the last resume.  Returns (offset, idev); dev.reset_ is always false afterwards.
 struct F2 { float x, y; };
 
-M17B_FN_COLD F2 update_values(uint32_t* sb, const float* ring, int si, int pp, int ph, bool dev_reset)
+M17B_FN_COLD F2 update_values(uint32_t* sb, const LaneIo& e, int si, int pp, uint32_t p, int k, bool dev_reset)
 {
     float min_sum = 0, max_sum = 0;
     int min_count = 0, max_count = 0;
@@ -274,7 +331,7 @@ M17B_FN_COLD F2 update_values(uint32_t* sb, const float* ring, int si, int pp, i
     for (int i = si; i < 80; i += 10) {
         int d = pp - i;
         d = d < 0 ? d + 80 : d;
-        lv[n++] = ring_back(ring, ph, d);
+        lv[n++] = y_back(e, p, k, d);
     }
     float min_level = lv[0], max_level = lv[0];
     for (int i = 0; i != n; ++i) {
@@ -321,11 +378,6 @@ M17B_FN_COLD F2 clock_update_index(uint32_t* sb, int ssi, uint32_t ck_count)
     kf_store(sb, F_CK_X0, k);
     F2 r; r.x = k.x0; r.y = k.x1;
     return r;
-}
-
-M17B_FN size_t ring_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
-{
-    return ((size_t) ((p >> 5) & lmask) * np + s) * kLine + (p & (kLine - 1));
 }
 
 // apps/m17-demod.cpp:489: float(double(sample) / 41067.0)
@@ -393,51 +445,83 @@ M17B_FN uint32_t llr4(const LlrTable& tab, float sample)
 // scan
 // ---------------------------------------------------------------------------
 
+// One 8-sample block of ring_y as a lane holds it while it walks the block.
+struct Blk {
+    float y[8];
+    Biquad start;          // limit-filter history before block sample jb
+    uint32_t base;         // ring position of y[0]
+    int jb;                // first sample of the block this pass clocks
+};
+
+M17B_FN float y_sel(const float (&y)[8], int j)
+{
+    const float a = (j & 1) ? y[1] : y[0], b = (j & 1) ? y[3] : y[2], c = (j & 1) ? y[5] : y[4], d = (j & 1) ? y[7] : y[6];
+    const float ab = (j & 2) ? b : a, cd = (j & 2) ? d : c;
+    return (j & 4) ? cd : ab;
+}
+
+// limit_ after block sample j (Correlator.h:45): the block's filter steps jb .. j again
+M17B_FN float limit_at(const Blk& b, int j)
+{
+    Biquad q = b.start;
+    float r = 0.f;
+#pragma unroll
+    for (int i = 0; i != 8; ++i)
+        if (i >= b.jb && i <= j) r = limit_step(q, b.y[i]);
+    return r;
+}
+
 // Per-lane working set of the scan.
 struct Scan {
     float level;                               // DCD level (the sliding DFT and its energy sums live in dcd_lane)
-    float iir0, iir1, limit;                   // limit biquad history / output
+    Biquad bq;                                 // limit filter history (Correlator::sample_filter)
     float idev, offset, evm;
     float ck_est, ck_sest;
     uint32_t ck_count;
     int count, init;
-    int corr_pos, rp, framer_index, gap_k;     // next logical / physical ring write slot
-    int pp, ph;                                // logical / physical slot of the sample being handled
+    int corr_pos, i10, framer_index, gap_k;    // logical slot (0..79) the next clocked sample goes to, and that modulo 10
+    int pp;                                    // logical slot of the sample being handled
+    uint32_t p;                                // its ring position
+    int k;                                     // samples clocked since the last resume, counting it (<= kTapsUsed)
     int state, swt, si, ssi, csi;
     bool dcd, dcd_trig, need_reset, need_update, dev_reset, eot, pending;
     int sync_count, missing;
     uint32_t vcost;
     uint32_t sw;                               // packed SyncWord state, 8 bits per word
+    // where the sample being handled gets its sync-word trigger decisions from
+    float limit;                               // block walk: limit_ after it, recomputed from the block's samples when first asked for
+    bool have_limit;
+    uint32_t mbits;                            // search walk: the search pass's trigger bits of this sample (bit w = sync word w)
 };
 
-struct LaneIo {
-    const LlrTable* llr_tab;
-    uint32_t* sb;          // &st[block][0][lane]
-    float* ring;           // [96] column, stride RS (shared memory on the device)
-    float* lim;            // [8] column, stride RS: limit after each sample of the current block
-    float* ring_base;      // column 0 of the CTA's rings / limits and this lane's column number:
-    float* lim_base;       //   lanes read each other's columns when they share a search (corr_bit)
-    int col;
-    float* sw_samples;     // + s, stride np
-    int16_t* llr;          // + s, stride np
-    float* snap;           // + s, stride np
-    const float* ring_y;
-    const float* ring_d;
-    const int16_t* ring_x;
-    uint32_t np, lmask, s;
-};
+// SyncWord::triggered() for the sample being handled, block walk
+M17B_FN float sync_value(Scan& z, const LaneIo& e, const Blk& b, uint32_t word, float m1, float m2)
+{
+    if (!z.have_limit) {
+        z.limit = limit_at(b, (int) (z.p - b.base));
+        z.have_limit = true;
+    }
+    return sync_triggered(e, z.p, z.k, z.limit, word, m1, m2);
+}
+
+// ... search walk (w: 0 preamble, 1 LSF / stream, 2 packet / BERT): the decision is the search pass's, the
+// value the same correlation
+M17B_FN float sync_value_masked(const Scan& z, const LaneIo& e, int w, uint32_t word)
+{
+    return ((z.mbits >> w) & 1u) ? correlate(e, z.p, z.k, word) : 0.f;
+}
 
 #define M17B_UPDATE_VALUES(index_)                                                  \
     do {                                                                            \
-        F2 od_ = update_values(e.sb, e.ring, z.si, z.pp, z.ph, z.dev_reset);        \
+        F2 od_ = update_values(e.sb, e, z.si, z.pp, z.p, z.k, z.dev_reset);         \
         z.offset = od_.x; z.idev = od_.y; z.dev_reset = false;                      \
         z.ssi = (index_);                                                           \
     } while (0)
 
-M17B_FN int do_sync_step(Scan& z, const LaneIo& e, int k, uint32_t word, float m1, float m2, int* timing)
+M17B_FN int do_sync_step(Scan& z, const LaneIo& e, int k, float value /* SyncWord::triggered() */, int* timing)
 {
     uint32_t f = (z.sw >> (8 * k)) & 0xFF;
-    uint32_t r = sync_step(e.sw_samples + (size_t) (10 * k) * e.np, e.np, e.ring, z.ph, z.pp % 10, z.limit, word, m1, m2, f);
+    uint32_t r = sync_step(e.sw_samples + (size_t) (10 * k) * e.np, e.np, value, z.pp % 10, f);
     z.sw = (z.sw & ~(0xFFu << (8 * k))) | ((r & 0xFF) << (8 * k));
     *timing = (int) (r & 0xF);
     uint32_t u = (r >> 8) & 3;
@@ -472,13 +556,13 @@ M17B_FN void update_dcd(Scan& z, const LaneIo& e)
     }
 }
 
-// M17Demodulator.h:288-342
+// M17Demodulator.h:288-342 (search walk only: the trigger decisions are the search pass's)
 M17B_FN void do_unlocked(Scan& z, const LaneIo& e)
 {
     int timing;
     if (z.missing < 1920) {
         z.missing += 1;
-        int upd = do_sync_step(z, e, 0, kWordPreamble, 29.f, kLowest, &timing);
+        int upd = do_sync_step(z, e, 0, sync_value_masked(z, e, 0, kWordPreamble), &timing);
         if (upd) {
             z.sync_count = 0;
             z.missing = 0;
@@ -490,7 +574,7 @@ M17B_FN void do_unlocked(Scan& z, const LaneIo& e)
         }
         return;
     }
-    int upd = do_sync_step(z, e, 1, kWordLsf, 31.f, -31.f, &timing);
+    int upd = do_sync_step(z, e, 1, sync_value_masked(z, e, 1, kWordLsf), &timing);
     if (upd) {
         z.sync_count = 86;
         z.missing = 0;
@@ -501,7 +585,7 @@ M17B_FN void do_unlocked(Scan& z, const LaneIo& e)
         z.state = ST_FRAME;
         z.swt = upd < 0 ? SW_STREAM : SW_LSF;
     }
-    upd = do_sync_step(z, e, 2, kWordPacket, 31.f, -31.f, &timing);
+    upd = do_sync_step(z, e, 2, sync_value_masked(z, e, 2, kWordPacket), &timing);
     if (upd < 0) {
         z.sync_count = 86;
         z.missing = 0;
@@ -515,16 +599,16 @@ M17B_FN void do_unlocked(Scan& z, const LaneIo& e)
 }
 
 // M17Demodulator.h:349-411 (only called on samples with index() == sample_index)
-M17B_FN void do_lsf_sync(Scan& z, const LaneIo& e)
+M17B_FN void do_lsf_sync(Scan& z, const LaneIo& e, const Blk& b)
 {
-    float trig = sync_triggered(e.ring, z.ph, z.limit, kWordPreamble, 29.f, kLowest);
+    float trig = sync_value(z, e, b, kWordPreamble, 29.f, kLowest);
     if ((double) trig > 0.1) {
         z.need_update = true;
         z.sync_count += 1;
         return;
     }
-    trig = sync_triggered(e.ring, z.ph, z.limit, kWordLsf, 31.f, -31.f);
-    float bert = sync_triggered(e.ring, z.ph, z.limit, kWordPacket, 31.f, -31.f);
+    trig = sync_value(z, e, b, kWordLsf, 31.f, -31.f);
+    float bert = sync_value(z, e, b, kWordPacket, 31.f, -31.f);
     if (bert < 0) {
         z.missing = 0;
         z.sync_count = 86;
@@ -555,9 +639,9 @@ M17B_FN void do_lsf_sync(Scan& z, const LaneIo& e)
 }
 
 // M17Demodulator.h:419-482 past the `sync_count < MIN_SYNC_COUNT` gate
-M17B_FN void do_stream_sync(Scan& z, const LaneIo& e)
+M17B_FN void do_stream_sync(Scan& z, const LaneIo& e, const Blk& b)
 {
-    if (sync_triggered(e.ring, z.ph, z.limit, kWordEot, 31.f, kLowest) > 0.1f) {
+    if (sync_value(z, e, b, kWordEot, 31.f, kLowest) > 0.1f) {
         z.swt = SW_STREAM;
         z.state = ST_FRAME;
         z.eot = true;
@@ -565,7 +649,7 @@ M17B_FN void do_stream_sync(Scan& z, const LaneIo& e)
         return;
     }
     int timing;
-    int upd = do_sync_step(z, e, 1, kWordLsf, 31.f, -31.f, &timing);
+    int upd = do_sync_step(z, e, 1, sync_value(z, e, b, kWordLsf, 31.f, -31.f), &timing);
     if (upd < 0) {
         z.missing = 0;
         M17B_UPDATE_VALUES(timing);
@@ -593,10 +677,10 @@ M17B_FN void do_stream_sync(Scan& z, const LaneIo& e)
 }
 
 // M17Demodulator.h:488-530 (packet) and :535-574 (BERT) past the MIN_SYNC_COUNT gate
-M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, bool bert)
+M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, const Blk& b, bool bert)
 {
     int timing;
-    int upd = do_sync_step(z, e, 2, kWordPacket, 31.f, -31.f, &timing);
+    int upd = do_sync_step(z, e, 2, sync_value(z, e, b, kWordPacket, 31.f, -31.f), &timing);
     int swt = bert ? SW_BERT : SW_PACKET;
     if (bert ? (upd < 0) : (upd != 0)) {
         z.missing = 0;
@@ -620,7 +704,7 @@ M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, bool bert)
 }
 
 // M17Demodulator.h:595-654 up to the decoder call (which decode_kernel performs)
-M17B_FN void do_frame(Scan& z, const LaneIo& e, int idx /* index() of this sample = pp % 10 */)
+M17B_FN void do_frame(Scan& z, const LaneIo& e, const Blk& b, int idx /* index() of this sample = pp % 10 */)
 {
     int diff = z.si - idx;
     if (diff == 5 || diff == -5) {
@@ -643,7 +727,7 @@ M17B_FN void do_frame(Scan& z, const LaneIo& e, int idx /* index() of this sampl
     }
     if (idx != z.si) return;
 
-    float sample = e.ring[z.ph * RS] - z.offset;
+    float sample = y_sel(b.y, (int) (z.p - b.base)) - z.offset;
     sample *= z.idev;                                   // polarity is +1 and never changes
     // SymbolEvm.h:31-51 + StandardDeviation.h:68-72
     float err;
@@ -665,54 +749,19 @@ M17B_FN void do_frame(Scan& z, const LaneIo& e, int idx /* index() of this sampl
     z.state = ST_TBD;
 }
 
-// Sync-word trigger masks of one 8-sample block: bit 8 w + j is set when sync word w
-// (0 preamble, 1 LSF/stream, 2 packet/BERT, 3 EOT) triggers on block sample j
-// (Correlator.h:150-157 returns non-zero).  Computed by corr_masks(); kNoMasks = not computed.
-constexpr uint64_t kNoMasks = ~0ull;
-
 M17B_FN bool sw_trig(const Scan& z, int k) { return (z.sw >> (8 * k + 4)) & 1; }
 
-// block-sample index of the first set bit at or after j, 8 if none
-M17B_FN int next_bit(uint32_t m8, int j)
+// Number of upcoming samples on which the state machine provably does nothing but count, for the
+// states the block walk handles (every state but UNLOCKED): `i10` = index() of the next sample.
+// advance_quiet() applies the counting.
+M17B_FN int quiet_samples(const Scan& z, int i10)
 {
-    uint32_t m = (m8 & 0xFFu) >> j;
-    return m ? j + first_set(m) : 8;
-}
-
-// Number of upcoming samples on which the state machine provably does nothing but
-// count: `i10` = index() of the next sample, j its offset in the block, `masks` the
-// block's trigger masks.  advance_quiet() applies the counting.
-M17B_FN int quiet_samples(const Scan& z, int i10, int j, uint64_t masks)
-{
-    const bool have = masks != kNoMasks;
-    const uint32_t mk = (uint32_t) masks;
     int q;
     switch (z.state) {
-    case ST_UNLOCKED:                                                              // :288-342 looks for a sync word on every sample
-        if (!have) return 0;
-        if (z.missing < 1920) {
-            if (sw_trig(z, 0)) return 0;
-            q = next_bit(mk, j) - j;
-            int lim = 1920 - z.missing;                                            // then the search changes words
-            q = q < lim ? q : lim;
-        } else {
-            if (sw_trig(z, 1) || sw_trig(z, 2)) return 0;
-            q = next_bit((mk >> 8) | (mk >> 16), j) - j;
-        }
-        break;
     case ST_LSF_SYNC: { int d = z.si - i10; q = d < 0 ? d + 10 : d; break; }       // acts when index() == sample_index
-    case ST_STREAM_SYNC: case ST_PACKET_SYNC: case ST_BERT_SYNC: {
+    case ST_STREAM_SYNC: case ST_PACKET_SYNC: case ST_BERT_SYNC:
         q = 77 - z.sync_count; q = q < 0 ? 0 : q;                                  // ++sync_count; acts from 78 on
-        const int k = z.state == ST_STREAM_SYNC ? 1 : 2;
-        if (have && !sw_trig(z, k) && j + q < 8) {
-            // inside the window a sample still does nothing unless a word triggers or sync_count passes 86
-            uint32_t m = z.state == ST_STREAM_SYNC ? ((mk >> 8) | (mk >> 24)) : (mk >> 16);
-            int qb = next_bit(m, j + q) - j;
-            int qt = 86 - z.sync_count; qt = qt < 0 ? 0 : qt;
-            q = qb < qt ? qb : qt;
-        }
         break;
-    }
     case ST_SYNC_WAIT: q = z.sync_count < 86 ? 86 - z.sync_count : 0; break;       // ++sync_count up to 86, then acts
     case ST_FRAME: {
         int d = z.si - i10; d = d < 0 ? d + 10 : d;                                // samples until index() == sample_index
@@ -738,22 +787,21 @@ M17B_FN void advance_quiet(Scan& z, int n)
         z.missing += n;                                // :291-293
 }
 
-// Trigger masks for the block of the lane whose ring / limit columns are given: helper t of 32
-// evaluates sync word t >> 3 on block sample t & 7 (ph0 = physical ring slot of block sample 0)
-// with exactly the arithmetic of sync_triggered().
-M17B_FN bool corr_bit(const float* ring, const float* lim, int ph0, int t)
+// n more samples go through the correlator (Correlator.h:43-49: buffer position; the filter's own age)
+M17B_FN void clocked(Scan& z, int n)
 {
-    const int w = t >> 3, j = t & 7;
-    int ph = ph0 + j; ph = ph >= kRing ? ph - kRing : ph;
-    const uint32_t word = w == 0 ? kWordPreamble : w == 1 ? kWordLsf : w == 2 ? kWordPacket : kWordEot;
-    const float m1 = w == 0 ? 29.f : 31.f;
-    const float m2 = (w == 0 || w == 3) ? kLowest : -31.f;
-    return sync_triggered(ring, ph, lim[j * RS], word, m1, m2) != 0;
+    z.gap_k = z.gap_k + n < kTapsUsed ? z.gap_k + n : kTapsUsed;
+    if (n < 10) {
+        z.corr_pos += n; if (z.corr_pos >= 80) z.corr_pos -= 80;
+        z.i10 += n; if (z.i10 >= 10) z.i10 -= 10;
+    } else {
+        z.corr_pos = (z.corr_pos + n) % 80;
+        z.i10 = z.corr_pos % 10;
+    }
 }
 
-// One sample of M17Demodulator.h:695-740 (everything between correlator.sample()
-// and the carrier-detect cadence check).
-M17B_FN void event_step(Scan& z, const LaneIo& e, int i10 /* z.pp % 10 */)
+// M17Demodulator.h:695-712: clock recovery reset / update when index() == 0, then clock_recovery(sample)
+M17B_FN void clock_gate(Scan& z, const LaneIo& e, int i10 /* z.pp % 10 */)
 {
     uint32_t* sb = e.sb;
     if (i10 == 0) {               // :695-709
@@ -775,27 +823,33 @@ M17B_FN void event_step(Scan& z, const LaneIo& e, int i10 /* z.pp % 10 */)
         }
     }
     z.ck_count++;                       // clock_recovery(filtered_sample), :712
+}
 
+// One sample of M17Demodulator.h:695-740 (everything between correlator.sample() and the carrier-detect
+// cadence check) in the states the block walk handles.
+M17B_FN void event_step(Scan& z, const LaneIo& e, const Blk& b, int i10 /* z.pp % 10 */)
+{
+    clock_gate(z, e, i10);
     switch (z.state) {                  // :714-740
-    case ST_UNLOCKED: do_unlocked(z, e); break;
-    case ST_LSF_SYNC: if (i10 == z.si) do_lsf_sync(z, e); break;
+    case ST_UNLOCKED: break;            // never here: the search walk's
+    case ST_LSF_SYNC: if (i10 == z.si) do_lsf_sync(z, e, b); break;
     case ST_STREAM_SYNC:
         z.sync_count += 1;
-        if (z.sync_count >= 78) do_stream_sync(z, e);
+        if (z.sync_count >= 78) do_stream_sync(z, e, b);
         break;
     case ST_PACKET_SYNC:
         z.sync_count += 1;
-        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, false);
+        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, b, false);
         break;
     case ST_BERT_SYNC:
         z.sync_count += 1;
-        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, true);
+        if (z.sync_count >= 78) do_packet_or_bert_sync(z, e, b, true);
         break;
     case ST_SYNC_WAIT:                  // :582-593
         if (z.sync_count < 86) z.sync_count += 1;
         else { z.need_update = true; z.state = ST_FRAME; }
         break;
-    default: do_frame(z, e, i10); break;
+    default: do_frame(z, e, b, i10); break;
     }
 }
 
@@ -807,62 +861,6 @@ M17B_FN void load_chunk(Chunk& c, const LaneIo& e, uint32_t base)
     const float4* py = reinterpret_cast<const float4*>(e.ring_y + o);
     float4 a0 = py[0], a1 = py[1];
     c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
-}
-
-// Dense pass over samples [jb, je) of the block starting at absolute position `base`: the per-sample
-// recurrences of the clocked path (the carrier detect's sliding DFT, which runs on every sample whatever
-// the state, is dcd_lane's).
-M17B_FN void dense_block(Scan& z, const LaneIo& e, const Chunk& c, int jb, int je, bool clocked, uint32_t base)
-{
-    if (!clocked) return;               // :675-689: the filter and the correlator are not clocked while !dcd_
-    if (jb == 0 && je == 8 && z.rp <= kRing - 8) {
-        // whole block, no ring wrap inside it: same arithmetic without the per-sample bookkeeping
-        float h1 = z.iir0, h2 = z.iir1;
-        float* ring = e.ring + z.rp * RS;
-#pragma unroll
-        for (int j = 0; j != 8; ++j) {
-            float h0 = fabsf(c.y[j]);
-            h0 -= -1.98148851f * h1;
-            h0 -= 0.98165828f * h2;
-            float r = 0.f;
-            r += 4.24433681e-05f * h0;
-            r += 8.48867363e-05f * h1;
-            r += 4.24433681e-05f * h2;
-            ring[j * RS] = c.y[j];
-            e.lim[j * RS] = r;
-            h2 = h1; h1 = h0;
-            if (j == 7) z.limit = r;
-        }
-        z.iir0 = h1; z.iir1 = h2;
-        z.gap_k = z.gap_k + 8 < kTapsUsed ? z.gap_k + 8 : kTapsUsed;
-        z.rp = z.rp == kRing - 8 ? 0 : z.rp + 8;
-        z.corr_pos = z.corr_pos >= 72 ? z.corr_pos - 72 : z.corr_pos + 8;
-        return;
-    }
-#pragma unroll
-    for (int j = 0; j != 8; ++j) {
-        if (j < jb || j >= je) continue;
-        // the matched filter has run speculatively on every sample; the 149 outputs after a
-        // carrier-detect gap have been replaced by fixup_kernel before the lane gets here
-        float filtered = c.y[j];
-        z.gap_k = z.gap_k < kTapsUsed ? z.gap_k + 1 : z.gap_k;
-        {   // correlator.sample(): Correlator.h:43-49, IirFilter.h:26-42
-            float h2 = z.iir1, h1 = z.iir0;
-            float h0 = fabsf(filtered);
-            h0 -= -1.98148851f * h1;
-            h0 -= 0.98165828f * h2;
-            float r = 0.f;
-            r += 4.24433681e-05f * h0;
-            r += 8.48867363e-05f * h1;
-            r += 4.24433681e-05f * h2;
-            z.limit = r;
-            z.iir0 = h0; z.iir1 = h1;
-            e.ring[z.rp * RS] = filtered;
-            e.lim[j * RS] = r;
-            z.rp = z.rp == kRing - 1 ? 0 : z.rp + 1;
-            z.corr_pos = z.corr_pos == 79 ? 0 : z.corr_pos + 1;
-        }
-    }
 }
 
 // ---------------------------------------------------------------------------
@@ -970,84 +968,163 @@ M17B_FN void dcd_sums(const DevPtrs& d, const LaneIo& e, uint32_t pos, uint32_t 
     l2 = p[d.np];
 }
 
-// Offset, from the next sample the event pass handles, of the last symbol instant of the frame being
-// received (ST_FRAME): `ahead` = samples the dense pass is ahead of the event pass, so that sample sits
-// at logical correlator position corr_pos - ahead; symbols are taken when index() == sample_index, 10
-// samples apart (the dead-reckoned sample_index moves by at most +-1 a few times per frame).
+// Offset, from the next sample the lane handles (logical slot corr_pos), of the last symbol instant of
+// the frame being received (ST_FRAME): symbols are taken when index() == sample_index, 10 samples apart
+// (the dead-reckoned sample_index moves by at most +-1 a few times per frame).
 constexpr int kDeferMarginFrame = 6;
 constexpr int kDeferMarginSync = 16;
-M17B_FN int frame_end_offset(int si, int corr_pos, int ahead, int framer_index)
+M17B_FN int frame_end_offset(int si, int i10, int framer_index)
 {
-    int pp = corr_pos - ahead;
-    while (pp < 0) pp += 80;
-    int dsi = si - pp % 10;
+    int dsi = si - i10;
     if (dsi < 0) dsi += 10;
     return dsi + (183 - (framer_index >> 1)) * 10;
 }
 
-// Walk this lane from its position towards `head`; on return the lane is at head, stopped on
-// a completed frame (FL_PENDING, decode_kernel's turn), waiting for a filter fix-up (FL_FIXUP)
-// or out of budget.  Called by all 32 lanes of a warp together (`valid` = the lane has a stream):
-// the block loop is warp-synchronous so that the lanes can evaluate the sync-word correlations of
-// a searching lane's block between them (corr_bit).
+// The carrier detect gates the filter and the correlator off after the sample at pos - 1
+// (M17Demodulator.h:675-689): freeze what they would still hold when they resume.
+M17B_FN_COLD void gate_off(const DevPtrs& d, const LaneIo& e, int gap_k, uint32_t pos)
+{
+    take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, gap_k);
+    // Correlator::buffer_: the last 80 clocked samples, oldest first.  The carrier detect stays on for at
+    // least 960 samples (and the start-up clocks 1920), so they are all ring samples.
+    if (gap_k < 80) ctr_add(&d.ctr->faults, 1ull);
+    for (int j = 0; j != 80; ++j)
+        e.csnap[(size_t) j * e.np] = e.ring_y[ring_off(pos - 80u + (uint32_t) j, e.lmask, e.np, e.s)];
+}
+
+// First sample in [p, p + n) on which one of the selected sync words triggers according to the search
+// pass's masks, as an offset from p; n if there is none.  sel: bits 8 w .. 8 w + 7 set for every wanted word w.
+M17B_FN int next_trigger(const LaneIo& e, uint32_t p, int n, uint32_t sel)
+{
+    int done = 0;
+    while (done < n) {
+        const uint32_t q = p + (uint32_t) done;
+        const uint4 v = *reinterpret_cast<const uint4*>(e.mask_ring + ((size_t) ((q >> 5) & e.lmask) * e.np + e.s) * 4);
+        const uint32_t w0 = v.x & sel, w1 = v.y & sel, w2 = v.z & sel, w3 = v.w & sel;
+        uint32_t lm = ((w0 | (w0 >> 8) | (w0 >> 16) | (w0 >> 24)) & 0xFFu) | (((w1 | (w1 >> 8) | (w1 >> 16) | (w1 >> 24)) & 0xFFu) << 8) |
+                      (((w2 | (w2 >> 8) | (w2 >> 16) | (w2 >> 24)) & 0xFFu) << 16) | (((w3 | (w3 >> 8) | (w3 >> 16) | (w3 >> 24)) & 0xFFu) << 24);
+        lm >>= (q & 31u);
+        if (lm) {
+            const int o = done + first_set(lm);
+            return o < n ? o : n;
+        }
+        done += 32 - (int) (q & 31u);
+    }
+    return n;
+}
+
+// the four trigger bits (bit w = sync word w) the search pass recorded for the sample at p
+M17B_FN uint32_t mask_bits(const LaneIo& e, uint32_t p)
+{
+    const uint32_t m = e.mask_ring[blk_off(p, e.lmask, e.np, e.s)] >> (p & 7u);
+    return (m & 1u) | ((m >> 7) & 2u) | ((m >> 14) & 4u) | ((m >> 21) & 8u);
+}
+
+// Bring the limit filter from position `from` (where z.bq is valid) to `to` inside a searched span: the
+// search pass left the filter history at every block end it covered (ckpt_ring).
+M17B_FN void bq_catch_up(Scan& z, const LaneIo& e, uint32_t from, uint32_t to)
+{
+    if (from == to) return;
+    uint32_t start = from;
+    const uint32_t tb = to & ~7u;
+    if ((int32_t) (tb - from) > 0) {
+        const float2 c = e.ckpt_ring[blk_off(tb - 8u, e.lmask, e.np, e.s)];
+        z.bq.h1 = c.x; z.bq.h2 = c.y;
+        start = tb;
+    }
+    for (uint32_t p = start; p != to; ++p) limit_step(z.bq, e.ring_y[ring_off(p, e.lmask, e.np, e.s)]);
+}
+
+// Diagnostics at the reference's update points (M17Demodulator.h:675-689 while !dcd_: evm argument is
+// dev.error() = 0, FreqDevEstimator.h:53; :742-752 while dcd_: evm.evm()), only when the context records them.
+M17B_FN_COLD void emit_diag_rec(const DevPtrs& d, uint32_t s, const m17b_diag& v)
+{
+    const uint32_t slot = ctr_add(&d.ctr->diag_count, 1u);
+    if (slot - d.diag_read >= d.diag_cap) { ctr_add(&d.ctr->diag_dropped, 1ull); return; }
+    m17b_diag_rec* r = d.diag_recs + (slot & (d.diag_cap - 1));
+    r->stream = s; r->pad = 0;
+    r->d = v;
+}
+
+M17B_FN void emit_diag(const DevPtrs& d, const LaneIo& e, const Scan& z, unsigned long long samples, bool locked_path)
+{
+    if (!d.diag_recs) return;
+    m17b_diag v;
+    v.dcd = z.dcd ? 1 : 0;
+    v.evm = locked_path ? sqrtf(z.evm) : 0.f;            // SymbolEvm::evm(), StandardDeviation.h:79-82
+    v.deviation = 2400.f / z.idev;                       // FreqDevEstimator.h:52
+    v.offset = z.offset;
+    v.locked = z.state != ST_UNLOCKED;
+    v.clock = z.ck_est;
+    v.sample_index = z.si; v.sync_index = z.ssi; v.clock_index = z.csi;
+    v.viterbi_cost = (int32_t) z.vcost;
+    v.samples = samples;
+    emit_diag_rec(d, e.s, v);
+}
+
+// Walk this lane from its position towards `head`; on return the lane is at head, stopped on a completed
+// frame (FL_PENDING, decode_kernel's turn), waiting for fixup_kernel (FL_FIXUP: matched-filter outputs after a
+// carrier-detect gap and / or a sync-word search over the samples ahead), or has left a partial frame for
+// the next submit (M17B_STREAMING).  Three ways of walking:
+//   idle    carrier detect off: nothing is clocked; jump from one 384-sample update to the next;
+//   search  ST_UNLOCKED with the carrier detect on: the state machine looks for sync words on every sample.
+//           fixup_kernel's search pass evaluates the limit filter and the correlations for the whole span at
+//           once (one thread per sample) and leaves trigger masks; the lane jumps from trigger to trigger;
+//   block   every other state (and the 1920-sample start-up): aligned 8-sample blocks of ring_y; the limit
+//           filter runs densely over the block in registers, the state machine only on the samples it can
+//           act on (quiet_samples() gives the distance in closed form).
 M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigned long long head64, bool valid, bool defer,
                        uint32_t guard = 0 /* samples a concurrent filter launch may be writing past head */)
 {
+    if (!valid) return;
     uint32_t* sb = e.sb;
-    uint32_t pos = valid ? sb[F_POS * 32] : head;
-    uint32_t fl = valid ? sb[F_FLAGS * 32] : 0u;
-    bool active = pos != head && !(fl & (FL_PENDING | FL_FIXUP));
+    uint32_t pos = sb[F_POS * 32];
+    uint32_t fl = sb[F_FLAGS * 32];
+    if (pos == head) return;
+    if (fl & (FL_PENDING | FL_FIXUP)) { ctr_add(&d.ctr->lagging, 1u); return; }
     // Deferral (rounds enqueued by m17b_submit; m17b_sync's flush rounds run every lane to the head): a lane
     // whose current frame cannot complete before the head leaves the rest of the chunk for the next submit.
     // The records are the same -- every frame that ends inside this chunk is still completed here -- but the
     // lane then walks one whole frame per round together with its neighbours, instead of a partial frame
-    // after its last completion and another one at the start of the next chunk, each at half the lanes
-    // and each paying the round's serial latency (two of a submit's rounds, profiles/r01q).
+    // after its last completion and another one at the start of the next chunk.
     // In ST_FRAME the end of the frame is known to +-2 samples (frame_end_offset); right after a frame, while
     // the next sync word is awaited, only to -11 .. +5 (a re-timed sync word moves the symbol phase), hence
     // the wider margin there -- a lane inside that margin starts walking and is stopped by the same test a
-    // few blocks later, once it is in ST_FRAME (block loop below).
-    bool deferred = false;
-    if (active && defer) {
+    // few blocks later, once it is in ST_FRAME (block walk below).
+    if (defer) {
         const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
         const long long left = (long long) (head - pos);
+        bool deferred = false;
         if (st == ST_FRAME) {
             const uint32_t idx = sb[F_IDX * 32];
-            const int eo = frame_end_offset((int) ((fl >> FL_SI_SHIFT) & 15), (int) (idx & 0xFF),
-                                            (int) (sb[F_DPOS * 32] - pos), (int) ((idx >> 8) & 0xFFFF));
+            const int eo = frame_end_offset((int) ((fl >> FL_SI_SHIFT) & 15), (int) (idx & 0xFF) % 10, (int) ((idx >> 8) & 0xFFFF));
             if ((long long) eo - kDeferMarginFrame >= left) deferred = true;
         } else if (st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT) {
             // sync_count counts samples from the last frame's end; frames are 1920 samples apart
             if (1919ll - (long long) sb[F_SYNC_COUNT * 32] - kDeferMarginSync >= left) deferred = true;
         }
-        if (deferred) active = false;
+        if (deferred) { ctr_add(&d.ctr->deferred, 1u); return; }
     }
-    if (pos != head && !active && !deferred) ctr_add(&d.ctr->lagging, 1u);
     // a stream that fell so far behind that the sample ring has wrapped over what it still needs
     // (submits enqueued back to back without m17b_sync and more stops than rounds): must never happen
     if (head + guard - pos > d.ring_lines * (uint32_t) kLine - 176u) ctr_add(&d.ctr->faults, 1ull);
-    const bool loaded = active;
-    uint32_t dpos = pos;
-    uint32_t gap_r = 0;                                     // position the filter last resumed at
-    int gap_done = 0;                                       // outputs after it already corrected
-    bool fixup = false;
+
+    uint32_t gap_r = sb[F_GAPR * 32];                       // position the filter last resumed at
+    int gap_done = (int) sb[F_GAPDONE * 32];                // outputs after it already corrected
+    uint32_t sfrom = sb[F_SFROM * 32], sto = sb[F_STO * 32];    // span the search pass has covered
+    bool fixup = false, deferred = false;
 
     Scan z;
     memset(&z, 0, sizeof(z));
-    if (active) {
-    dpos = sb[F_DPOS * 32];
-    gap_r = sb[F_GAPR * 32];
-    gap_done = (int) sb[F_GAPDONE * 32];
     z.level = u2f(sb[F_LEVEL * 32]);
-    z.iir0 = u2f(sb[F_IIR0 * 32]); z.iir1 = u2f(sb[F_IIR1 * 32]);
-    z.limit = u2f(sb[F_LIMIT * 32]);
+    z.bq.h1 = u2f(sb[F_IIR0 * 32]); z.bq.h2 = u2f(sb[F_IIR1 * 32]);
     z.idev = u2f(sb[F_IDEV * 32]); z.offset = u2f(sb[F_OFFSET * 32]);
     z.evm = u2f(sb[F_EVM * 32]);
     z.ck_est = u2f(sb[F_CK_EST * 32]); z.ck_sest = u2f(sb[F_CK_SEST * 32]);
     z.ck_count = sb[F_CK_COUNT * 32];
     { uint32_t v = sb[F_CNT * 32]; z.count = v & 0xFFFF; z.init = v >> 16; }
     { uint32_t v = sb[F_IDX * 32]; z.corr_pos = v & 0xFF; z.framer_index = (v >> 8) & 0xFFFF; z.gap_k = v >> 24; }
-    z.rp = (int) sb[F_RP * 32];
+    z.i10 = z.corr_pos % 10;
     z.state = (fl >> FL_STATE_SHIFT) & 7; z.swt = (fl >> FL_SWT_SHIFT) & 3;
     z.si = (fl >> FL_SI_SHIFT) & 15; z.ssi = (fl >> FL_SSI_SHIFT) & 15; z.csi = (fl >> FL_CSI_SHIFT) & 15;
     z.dcd = fl & FL_DCD; z.dcd_trig = fl & FL_DCD_TRIG; z.need_reset = fl & FL_NEED_RESET;
@@ -1056,172 +1133,174 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     z.vcost = sb[F_VCOST * 32];
     z.sw = sb[F_SW * 32];
 
-    for (int k = 0; k != kRing; ++k) e.ring[k * RS] = d.corr_ring[(size_t) k * d.np + e.s];
-    if (dpos != pos)                                        // limits of the samples the dense pass ran ahead by
-        for (int j = (int) (pos & 7); j != 8; ++j) e.lim[j * RS] = d.lim_save[(size_t) j * d.np + e.s];
-    }
-
-    int budget = kRoundCap;
-    // pf always holds the block the dense pass needs next (requested one block of arithmetic earlier).
-    // There is deliberately no second, direct-load path inside the loop: ptxas gave such a path the same
-    // scoreboard as the prefetch, so the first use of the current block also waited for the prefetch
-    // that had just been issued (17 % of the kernel's stall samples, profiles/r01d).
-    Chunk pf;
-    uint32_t pf_base = dpos & ~7u;
-    memset(&pf, 0, sizeof(pf));
-    if (active) load_chunk(pf, e, pf_base);
-
-    while (warp_any(active)) {
-        uint32_t base = 0;
-        int jb_e = 0, je = 0, ph0 = 0;
-        bool initializing = false, go = false, need = false;
-
-        if (active && defer && z.state == ST_FRAME && head - pos < 1920u &&
-            frame_end_offset(z.si, z.corr_pos, (int) (dpos - pos), z.framer_index) - kDeferMarginFrame >= (int) (head - pos)) {
-            deferred = true;                                // this frame ends after the head: the next submit's
-            active = false;
+    while (pos != head && !z.pending && !fixup && !deferred) {
+        if (!z.init && !z.dcd) {
+            // ---- idle: M17Demodulator.h:675-689 ------------------------------------------------
+            const uint32_t left = head - pos;
+            const int n = (uint32_t) (384 - z.count) < left ? 384 - z.count : (int) left;
+            z.count += n;
+            pos += (uint32_t) n;
+            if (z.count == 384) {
+                float l1, l2;
+                dcd_sums(d, e, pos, head, head64, 384, l1, l2);
+                update_dcd(z, e);
+                dcd_update(z, l1, l2);
+                emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), false);
+                z.count = 0;
+                if (z.dcd) { gap_r = pos; gap_done = 0; sfrom = sto = pos; }   // the filter resumes with the next sample:
+                                                            // whatever was searched before the gap no longer applies
+            }
+            continue;
         }
-        if (active) {
-            base = pos & ~7u;
-            jb_e = (int) (pos - base);
-            const int jb_d = (int) (dpos - base);           // jb_e <= jb_d <= 8
-            const uint32_t left = head - base;
-            je = left < 8u ? (int) left : 8;
-            initializing = z.init != 0;                     // :667-673
-            const bool clocked = initializing || z.dcd;
-            go = true;
+        if (!z.init && z.state == ST_UNLOCKED) {
+            // ---- search: ST_UNLOCKED with the carrier detect on (M17Demodulator.h:288-342) ------
+            if (!(pos - sfrom < sto - sfrom)) {             // no masks for this position yet: fixup_kernel's turn
+                fixup = true;
+                sfrom = sto = pos;
+                break;
+            }
+            const uint32_t left = sto - pos;                // sto <= head
+            const int n = (uint32_t) (960 - z.count) < left ? 960 - z.count : (int) left;
+            const uint32_t pos0 = pos;
+            int j = 0;
+            while (j < n) {
+                int q;
+                if (z.missing < 1920) {
+                    if (sw_trig(z, 0)) q = 0;
+                    else {
+                        const int lim = 1920 - z.missing;   // then the search changes words
+                        q = next_trigger(e, pos0 + (uint32_t) j, n - j < lim ? n - j : lim, 0x000000FFu);
+                    }
+                } else {
+                    if (sw_trig(z, 1) || sw_trig(z, 2)) q = 0;
+                    else q = next_trigger(e, pos0 + (uint32_t) j, n - j, 0x00FFFF00u);
+                }
+                if (z.need_reset || z.need_update) {        // :695-709 acts when index() == 0
+                    const int r = z.i10 == 0 ? 0 : 10 - z.i10;
+                    q = r < q ? r : q;
+                }
+                if (q >= n - j) { advance_quiet(z, n - j); clocked(z, n - j); j = n; break; }
+                if (q) { advance_quiet(z, q); clocked(z, q); j += q; }
+                z.p = pos0 + (uint32_t) j;
+                z.pp = z.corr_pos;
+                const int i10 = z.i10;
+                clocked(z, 1);
+                z.k = z.gap_k;
+                z.mbits = mask_bits(e, z.p);
+                clock_gate(z, e, i10);
+                do_unlocked(z, e);
+                ++j;
+                if (z.state != ST_UNLOCKED) break;
+            }
+            pos = pos0 + (uint32_t) j;
+            z.count += j;
+            bq_catch_up(z, e, pos0, pos);
+            if (z.count == 960) {                           // :742-752
+                float l1, l2;
+                dcd_sums(d, e, pos, head, head64, 960, l1, l2);
+                update_dcd(z, e);
+                z.count = 0;
+                emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), true);
+                dcd_update(z, l1, l2);
+                if (!z.dcd) gate_off(d, e, z.gap_k, pos);
+            }
+            continue;
+        }
 
-            if (jb_d < je && z.dcd && !initializing && z.gap_k < kTapsUsed) {
+        // ---- block walk ------------------------------------------------------------------------
+        // pf always holds the block the walk needs next (requested one block of arithmetic earlier)
+        Chunk pf;
+        load_chunk(pf, e, pos & ~7u);
+        for (;;) {
+            const uint32_t base = pos & ~7u;
+            const int jb = (int) (pos - base);
+            const uint32_t left = head - base;
+            const int je = left < 8u ? (int) left : 8;
+            const bool initializing = z.init != 0;          // :667-673
+            if (defer && z.state == ST_FRAME && !initializing && head - pos < 1920u &&
+                frame_end_offset(z.si, z.i10, z.framer_index) - kDeferMarginFrame >= (int) (head - pos)) {
+                deferred = true;                            // this frame ends after the head: the next submit's
+                break;
+            }
+            if (!initializing && z.gap_k < kTapsUsed) {
                 // outputs gap_k .. of the resumed filter are needed: are they corrected yet?
                 int k_last = (int) (base + (uint32_t) je - 1u - gap_r);
                 if (k_last > kTapsUsed - 1) k_last = kTapsUsed - 1;
-                if (k_last >= gap_done) {
-                    fixup = true;                           // fixup_kernel's turn
-                    d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
-                    go = false;
-                    active = false;
-                }
+                if (k_last >= gap_done) { fixup = true; break; }     // fixup_kernel's turn
             }
-            if (go && jb_d < je) {
-                // this block's samples were requested one iteration ago (the lane's next 32-byte sector of
-                // its own ring line); request the next block's before the arithmetic of this one
-                if (pf_base != base) ctr_add(&d.ctr->faults, 1ull);     // invariant: never happens
-                const Chunk c = pf;
-                pf_base = base + 8u;
-                load_chunk(pf, e, pf_base);
-                dense_block(z, e, c, jb_d, je, clocked, base);
-                const int n = je - jb_d;
-                if (initializing) z.init -= n;              // count_ stays 0 while initializing
-                else z.count += n;
-                dpos = base + (uint32_t) je;
+            Blk b;
+#pragma unroll
+            for (int i = 0; i != 8; ++i) b.y[i] = pf.y[i];
+            load_chunk(pf, e, base + 8u);                   // the next block's samples, before this block's arithmetic
+            b.base = base; b.jb = jb; b.start = z.bq;
+            // limit filter over the samples this pass clocks (Correlator.h:43-49)
+            if (jb == 0 && je == 8) {
+#pragma unroll
+                for (int i = 0; i != 8; ++i) limit_step(z.bq, b.y[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i != 8; ++i)
+                    if (i >= jb && i < je) limit_step(z.bq, b.y[i]);
             }
-            if (go && z.dcd && !initializing) {
-                // does the state machine look for sync words on (nearly) every sample of this block?
-                need = z.state == ST_UNLOCKED ||
-                       ((z.state == ST_STREAM_SYNC || z.state == ST_PACKET_SYNC || z.state == ST_BERT_SYNC) &&
-                        z.sync_count + (je - jb_e) >= 78);
-                ph0 = z.rp - (int) (dpos - base); if (ph0 < 0) ph0 += kRing;
-            }
-        }
-
-        // sync-word trigger masks for the lanes that search, one lane's block at a time: 4 words x 8
-        // samples = one correlation per helper lane
-        uint64_t masks = kNoMasks;
-        uint32_t todo = warp_ballot(need);
-        if (todo) {
-            warp_sync();                                    // the searching lanes' ring / limit columns are written
-            while (todo) {
-                const int L = first_set(todo);
-                todo &= todo - 1;
-                const int col = warp_bcast(e.col, L);
-                const int p0 = warp_bcast(ph0, L);
-#ifdef __CUDACC__
-                const uint32_t mk = warp_ballot(corr_bit(e.ring_base + col, e.lim_base + col, p0, lane_id()));
-#else
-                uint32_t mk = 0;
-                for (int t = 0; t != 32; ++t) mk |= (uint32_t) corr_bit(e.ring_base + col, e.lim_base + col, p0, t) << t;
-#endif
-                if (lane_id() == L) masks = mk;
-            }
-        }
-
-        if (go) {
             int j = je;
-            if (z.dcd && !initializing) {
-                // event pass over [jb_e, je): the sample at block offset j sits (dpos - base - j) slots
-                // behind the next write position
-                j = jb_e;
-                int back = (int) (dpos - base) - j;         // >= 1
-                z.pp = z.corr_pos - back; if (z.pp < 0) z.pp += 80;
-                z.ph = z.rp - back; if (z.ph < 0) z.ph += kRing;
-                int i10 = z.pp % 10;                        // index() of block sample j, kept in step with z.pp
+            if (initializing) {
+                const int n = je - jb;                      // count_ stays 0 while initializing
+                z.init -= n;
+                clocked(z, n);
+            } else {
+                j = jb;
                 while (j < je) {
-                    int q = quiet_samples(z, i10, j, masks);
-                    if (q >= je - j) { advance_quiet(z, je - j); j = je; break; }
-                    if (q) {
-                        advance_quiet(z, q);
-                        j += q;
-                        z.pp += q; if (z.pp >= 80) z.pp -= 80;
-                        z.ph += q; if (z.ph >= kRing) z.ph -= kRing;
-                        i10 += q; if (i10 >= 10) i10 -= 10;
-                    }
-                    z.limit = e.lim[j * RS];
-                    event_step(z, e, i10);
+                    const int q = quiet_samples(z, z.i10);
+                    if (q >= je - j) { advance_quiet(z, je - j); clocked(z, je - j); j = je; break; }
+                    if (q) { advance_quiet(z, q); clocked(z, q); j += q; }
+                    z.p = base + (uint32_t) j;
+                    z.pp = z.corr_pos;
+                    const int i10 = z.i10;
+                    clocked(z, 1);
+                    z.k = z.gap_k;
+                    z.have_limit = false;
+                    event_step(z, e, b, i10);
                     ++j;
-                    i10 = i10 == 9 ? 0 : i10 + 1;
-                    z.pp = z.pp == 79 ? 0 : z.pp + 1;
-                    z.ph = z.ph == kRing - 1 ? 0 : z.ph + 1;
-                    if (z.pending) break;
+                    if (z.pending || z.state == ST_UNLOCKED) break;
+                }
+                z.count += j - jb;
+                if (j != je) {                              // stopped inside the block: the filter history at that sample
+                    z.bq = b.start;
+#pragma unroll
+                    for (int i = 0; i != 8; ++i)
+                        if (i >= jb && i < j) limit_step(z.bq, b.y[i]);
                 }
             }
-            budget -= j - jb_e;
             pos = base + (uint32_t) j;
-
-            if (j == 8) {                                   // block complete: cadence checks
-                if (initializing) {
-                    if (z.init == 0) {                      // from the next sample on the filter is gated by !dcd_
-                        z.gap_k = kTapsUsed;
-                        take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, kTapsUsed);
-                    }
-                } else if (!z.dcd) {
-                    if (z.count == 384) {                   // :675-689
-                        float l1, l2;
-                        dcd_sums(d, e, pos, head, head64, 384, l1, l2);
-                        update_dcd(z, e);
-                        dcd_update(z, l1, l2);
-                        z.count = 0;
-                        if (z.dcd) { gap_r = pos; gap_done = 0; }   // the filter resumes with the next sample
-                    }
-                } else if (z.count == 960) {                // :742-752
-                    float l1, l2;
-                    dcd_sums(d, e, pos, head, head64, 960, l1, l2);
-                    update_dcd(z, e);
-                    z.count = 0;
-                    dcd_update(z, l1, l2);
-                    if (!z.dcd) take_snapshot(e.snap, e.ring_x, e.np, e.lmask, e.s, pos - 1, z.gap_k);
+            if (initializing) {
+                if (z.init == 0) {                          // from the next sample on the filter is gated by !dcd_
+                    z.gap_k = kTapsUsed;
+                    gate_off(d, e, z.gap_k, pos);
+                    break;
                 }
+            } else if (z.count == 960) {                    // :742-752
+                float l1, l2;
+                dcd_sums(d, e, pos, head, head64, 960, l1, l2);
+                update_dcd(z, e);
+                z.count = 0;
+                emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), true);
+                dcd_update(z, l1, l2);
+                if (!z.dcd) { gate_off(d, e, z.gap_k, pos); break; }
             }
-            active = pos != head && !z.pending && budget > 0;
+            if (pos == head || z.pending || z.state == ST_UNLOCKED) break;
         }
-    }
-    if (!loaded) {
-        if (deferred) ctr_add(&d.ctr->deferred, 1u);
-        return;
     }
 
     // write back
     sb[F_POS * 32] = pos;
-    sb[F_DPOS * 32] = dpos;
     sb[F_LEVEL * 32] = f2u(z.level);
-    sb[F_IIR0 * 32] = f2u(z.iir0); sb[F_IIR1 * 32] = f2u(z.iir1);
-    sb[F_LIMIT * 32] = f2u(z.limit);
+    sb[F_IIR0 * 32] = f2u(z.bq.h1); sb[F_IIR1 * 32] = f2u(z.bq.h2);
     sb[F_IDEV * 32] = f2u(z.idev); sb[F_OFFSET * 32] = f2u(z.offset);
     sb[F_EVM * 32] = f2u(z.evm);
     sb[F_CK_EST * 32] = f2u(z.ck_est); sb[F_CK_SEST * 32] = f2u(z.ck_sest);
     sb[F_CK_COUNT * 32] = z.ck_count;
     sb[F_CNT * 32] = (uint32_t) z.count | ((uint32_t) z.init << 16);
     sb[F_IDX * 32] = (uint32_t) z.corr_pos | ((uint32_t) z.framer_index << 8) | ((uint32_t) z.gap_k << 24);
-    sb[F_RP * 32] = (uint32_t) z.rp;
     fl = ((uint32_t) z.state << FL_STATE_SHIFT) | ((uint32_t) z.swt << FL_SWT_SHIFT) | ((uint32_t) z.si << FL_SI_SHIFT) |
          ((uint32_t) z.ssi << FL_SSI_SHIFT) | ((uint32_t) z.csi << FL_CSI_SHIFT) |
          (z.dcd ? FL_DCD : 0) | (z.dcd_trig ? FL_DCD_TRIG : 0) | (z.need_reset ? FL_NEED_RESET : 0) |
@@ -1232,9 +1311,10 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     sb[F_GAPDONE * 32] = (uint32_t) gap_done;
     sb[F_SYNC_COUNT * 32] = (uint32_t) z.sync_count; sb[F_MISSING * 32] = (uint32_t) z.missing;
     sb[F_SW * 32] = z.sw;
-    for (int k = 0; k != kRing; ++k) d.corr_ring[(size_t) k * d.np + e.s] = e.ring[k * RS];
-    if (dpos != pos)
-        for (int j = (int) (pos & 7); j != 8; ++j) d.lim_save[(size_t) j * d.np + e.s] = e.lim[j * RS];
+    // the searched span only means something while the search that asked for it goes on
+    if (!(z.state == ST_UNLOCKED && z.dcd && !z.init)) sfrom = sto = pos;
+    sb[F_SFROM * 32] = sfrom; sb[F_STO * 32] = sto;
+    if (fixup) d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
     if (z.pending) {
         // queue the frame by what M17FrameDecoder::operator() will do with it (M17FrameDecoder.h:353-392),
         // so that decode_kernel's warps each run one kind
@@ -1252,7 +1332,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
 
 // Fresh-demodulator state of one lane: the member initialisers of M17Demodulator
 // (M17Demodulator.h:148-178) and of its blocks; every other array starts zeroed.
-M17B_FN void init_lane(uint32_t* sb)
+M17B_FN void init_lane(uint32_t* sb, uint32_t pos0 = 0)
 {
     for (int f = 0; f != NFIELDS; ++f) sb[f * 32] = 0;
     Kalman k; kf_reset(k, 0.f);                              // KalmanFilter.h:28-31
@@ -1262,6 +1342,27 @@ M17B_FN void init_lane(uint32_t* sb)
     sb[F_IDX * 32] = (uint32_t) kTapsUsed << 24;             // no filter gap pending
     sb[F_FLAGS * 32] = FL_DEV_RESET | ((uint32_t) ST_UNLOCKED << FL_STATE_SHIFT) | ((uint32_t) SW_LSF << FL_SWT_SHIFT);
     sb[F_DEC * 32] = DEC_LSF;
+    // ring position of the stream's first sample (0 but for the wrap-around test hook)
+    sb[F_POS * 32] = pos0; sb[F_GAPR * 32] = pos0; sb[F_SFROM * 32] = pos0; sb[F_STO * 32] = pos0;
+}
+
+M17B_FN LaneIo make_io(const DevPtrs& d, uint32_t s, const LlrTable* tab)
+{
+    LaneIo e;
+    e.llr_tab = tab;
+    e.sb = d.st + st_index(s, 0);
+    e.sw_samples = d.sw_samples + s;
+    e.llr = d.llr + s;
+    e.snap = d.fir_snap + s;
+    e.csnap = d.corr_snap + s;
+    e.ring_y = d.ring_y;
+    e.ring_x = d.ring_x;
+    e.mask_ring = d.mask_ring;
+    e.ckpt_ring = d.ckpt_ring;
+    e.np = d.np;
+    e.lmask = d.ring_lines - 1;
+    e.s = s;
+    return e;
 }
 
 // Filter fix-up for one lane (host emulation: all outputs serially; the device kernel in
@@ -1275,6 +1376,7 @@ M17B_FN void fixup_lane(const DevPtrs& d, uint32_t s, uint32_t head)
     uint32_t avail = head - R;
     const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
     const uint32_t lmask = d.ring_lines - 1;
+    if (done >= upto) return;
     float xs[kTapsUsed];
     for (int m = 0; m < upto; ++m) xs[m] = scale_i16(d.ring_x[ring_off(R + (uint32_t) m, lmask, d.np, s)]);
     for (int k = done; k < upto; ++k) {
@@ -1290,7 +1392,57 @@ M17B_FN void fixup_lane(const DevPtrs& d, uint32_t s, uint32_t head)
         d.ring_y[ring_off(R + (uint32_t) k, lmask, d.np, s)] = y;
     }
     sb[F_GAPDONE * 32] = (uint32_t) upto;
-    sb[F_FLAGS * 32] &= ~FL_FIXUP;
+}
+
+// Does the lane that asked for fixup_kernel want a sync-word search over the samples ahead of it?
+// (ST_UNLOCKED with the carrier detect on, past the start-up: see scan_lane's search walk.)
+M17B_FN bool wants_search(const uint32_t* sb, uint32_t head)
+{
+    const uint32_t fl = sb[F_FLAGS * 32];
+    return ((fl >> FL_STATE_SHIFT) & 7u) == (uint32_t) ST_UNLOCKED && (fl & FL_DCD) && (sb[F_CNT * 32] >> 16) == 0 &&
+           sb[F_POS * 32] != head;
+}
+
+// One sample of the search pass: the limit filter step and the trigger decisions of the preamble, LSF /
+// stream and packet / BERT sync words (the words do_unlocked looks for, M17Demodulator.h:288-342) for the
+// sample at p, the k-th clocked one since the last resume.  Returns bit w = word w triggers.
+M17B_FN uint32_t search_sample(const LaneIo& e, Biquad& b, uint32_t p, int k)
+{
+    const float limit = limit_step(b, e.ring_y[ring_off(p, e.lmask, e.np, e.s)]);
+    float y8[8];
+#pragma unroll
+    for (int i = 0; i != 8; ++i) y8[i] = y_back(e, p, k, 70 - 10 * i);
+    return trigger_bits(limit, corr8(y8, kWordPreamble), corr8(y8, kWordLsf), corr8(y8, kWordPacket), 0.f);
+}
+
+// Search pass for one lane (host emulation: serially; the device kernel spreads it over a CTA): trigger
+// masks and limit-filter history at the block ends for [F_POS, head).  Leaves the lane's own state alone.
+M17B_FN void search_lane(const DevPtrs& d, uint32_t s, uint32_t head)
+{
+    uint32_t* sb = d.st + st_index(s, 0);
+    if (!wants_search(sb, head)) return;
+    const LaneIo e = make_io(d, s, nullptr);
+    const uint32_t from = sb[F_POS * 32];
+    Biquad b;
+    b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
+    int k = (int) (sb[F_IDX * 32] >> 24);
+    uint32_t word = 0;
+    for (uint32_t p = from; p != head; ++p) {
+        k = k < kTapsUsed ? k + 1 : k;
+        const uint32_t bits = search_sample(e, b, p, k);
+        const uint32_t j = p & 7u;
+        word |= ((bits & 1u) << j) | (((bits >> 1) & 1u) << (8 + j)) | (((bits >> 2) & 1u) << (16 + j));
+        if (j == 7u || p + 1u == head) {
+            d.mask_ring[blk_off(p, e.lmask, e.np, s)] = word;
+            word = 0;
+        }
+        if (j == 7u) {
+            float2 c; c.x = b.h1; c.y = b.h2;
+            d.ckpt_ring[blk_off(p, e.lmask, e.np, s)] = c;
+        }
+    }
+    sb[F_SFROM * 32] = from;
+    sb[F_STO * 32] = head;
 }
 
 // ---------------------------------------------------------------------------

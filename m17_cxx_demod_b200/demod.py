@@ -8,7 +8,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
-FIR_FMA, INVERT, PROFILE, STREAMING = 0x1, 0x2, 0x4, 0x8
+FIR_FMA, INVERT, PROFILE, STREAMING, DIAG_RECORDS = 0x1, 0x2, 0x4, 0x8, 0x10
 HOST, DEVICE = 0, 1
 
 FRAME_DTYPE = np.dtype([
@@ -16,6 +16,12 @@ FRAME_DTYPE = np.dtype([
     ("type", "u1"), ("pad", "u1", (3,)), ("payload", "u1", (26,)), ("lsf", "u1", (30,)),
 ])
 assert FRAME_DTYPE.itemsize == 80
+DIAG_REC_DTYPE = np.dtype([
+    ("stream", "<u4"), ("pad", "<u4"), ("dcd", "<i4"), ("evm", "<f4"), ("deviation", "<f4"), ("offset", "<f4"), ("locked", "<i4"),
+    ("clock", "<f4"), ("sample_index", "<i4"), ("sync_index", "<i4"), ("clock_index", "<i4"), ("viterbi_cost", "<i4"),
+    ("samples", "<u8"),
+])
+assert DIAG_REC_DTYPE.itemsize == 56
 FRAME_TYPE_NAMES = ["LSF", "LICH", "STREAM", "BASIC_PACKET", "FULL_PACKET", "BERT"]
 PAYLOAD_LEN = {0: 0, 1: 6, 2: 18, 3: 26, 4: 26, 5: 25}
 
@@ -72,7 +78,8 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_last_cuda_error.argtypes = [ctypes.c_void_p]
         lib.m17b_version.restype = ctypes.c_uint32
         for name in ("m17b_create", "m17b_submit", "m17b_sync", "m17b_drain", "m17b_pending_frames", "m17b_diag_get",
-                     "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_measure_fp32_peak",
+                     "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_debug_correlate", "m17b_diag_drain",
+                     "m17b_measure_fp32_peak",
                      "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count",
                      "m17b_event_record", "m17b_event_elapsed"):
             getattr(lib, name).restype = ctypes.c_int
@@ -99,6 +106,9 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_get_profile.argtypes = [ctypes.c_void_p, ctypes.POINTER(Profile), ctypes.c_int]
         lib.m17b_debug_filter.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
                                           ctypes.c_void_p, ctypes.c_void_p]
+        lib.m17b_debug_correlate.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
+                                             ctypes.c_void_p, ctypes.c_void_p]
+        lib.m17b_diag_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
         lib.m17b_event_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.m17b_event_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
         lib.m17b_measure_fp32_peak.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
@@ -139,10 +149,12 @@ class PinnedBuffer:
 class Demodulator:
     """N resident M17 streams on one GPU (m17b_ctx)."""
 
-    def __init__(self, n_streams: int, max_chunk: int, flags: int = 0, device: int = 0, frame_capacity: int = 0):
+    def __init__(self, n_streams: int, max_chunk: int, flags: int = 0, device: int = 0, frame_capacity: int = 0,
+                 debug_origin: int = 0):
         self._lib = load_library()
         cfg = _Config(n_streams=n_streams, device=device, max_chunk=max_chunk, flags=flags,
                       frame_capacity=frame_capacity)
+        cfg.reserved[0] = debug_origin & 0xFFFFFFFF      # test hook: ring position of the first sample
         self._ctx = ctypes.c_void_p()
         rc = self._lib.m17b_create(ctypes.byref(cfg), ctypes.byref(self._ctx))
         if rc:
@@ -264,6 +276,33 @@ class Demodulator:
                                                 y.ctypes.data_as(ctypes.c_void_p), x.ctypes.data_as(ctypes.c_void_p)),
                     "m17b_debug_filter")
         return y, x
+
+    def debug_correlate(self, samples: np.ndarray):
+        """Matched filter + correlator clocked on every sample of fresh streams: (filtered [n_streams, n],
+        corr [n_streams, n, 5] = limit_, preamble, LSF/stream, packet/BERT, EOT correlations)."""
+        samples = np.ascontiguousarray(samples, dtype=np.int16)
+        assert samples.shape[0] == self.n_streams
+        n = samples.shape[1]
+        y = np.zeros((self.n_streams, n), dtype=np.float32)
+        c = np.zeros((self.n_streams, n, 5), dtype=np.float32)
+        self._check(self._lib.m17b_debug_correlate(self._ctx, samples.ctypes.data_as(ctypes.c_void_p), n, n,
+                                                   y.ctypes.data_as(ctypes.c_void_p), c.ctypes.data_as(ctypes.c_void_p)),
+                    "m17b_debug_correlate")
+        return y, c
+
+    def diag_drain(self) -> np.ndarray:
+        """All diagnostic records so far (contexts created with DIAG_RECORDS), chronological within each stream."""
+        parts = []
+        cap = 4096
+        while True:
+            out = np.empty(cap, dtype=DIAG_REC_DTYPE)
+            got = ctypes.c_size_t()
+            self._check(self._lib.m17b_diag_drain(self._ctx, out.ctypes.data_as(ctypes.c_void_p), cap, ctypes.byref(got)),
+                        "m17b_diag_drain")
+            parts.append(out[:got.value])
+            if got.value < cap:
+                break
+        return np.concatenate(parts)
 
     def measure_fp32_peak(self, variant: int = 0) -> float:
         v = ctypes.c_double()

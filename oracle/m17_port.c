@@ -1205,6 +1205,23 @@ void m17port_correlator(const float* in, size_t n, uint8_t sample_index, float* 
     free(d);
 }
 
+/* Correlator.h:43-64 per sample: out5[5 i + 0] = limit_ after sample i, [1..4] = correlate() with the preamble,
+ * LSF / stream, packet / BERT and EOT sync words (M17Demodulator.h:154-157), correlator clocked on every sample. */
+void m17port_correlate_trace(const float* in, size_t n, float* out5)
+{
+    m17p_demod* d = (m17p_demod*) malloc(sizeof(m17p_demod));
+    m17p_init(d);
+    for (size_t i = 0; i != n; ++i) {
+        correlator_sample(d, in[i]);
+        out5[5 * i + 0] = d->corr_limit;
+        out5[5 * i + 1] = correlate(d, d->preamble_sync.word);
+        out5[5 * i + 2] = correlate(d, d->lsf_sync.word);
+        out5[5 * i + 3] = correlate(d, d->packet_sync.word);
+        out5[5 * i + 4] = correlate(d, d->eot_sync.word);
+    }
+    free(d);
+}
+
 void m17port_clock(const uint8_t* ops, const uint8_t* args, const uint32_t* dt, size_t n,
                    uint8_t* sample_index, float* clock_est, float* sample_est)
 {

@@ -118,6 +118,7 @@ float    m17port_scale(int16_t s);
 size_t   m17port_dcd(const float* in, size_t n, size_t period, float* level, uint8_t* trig);
 void     m17port_sdft(const float* in, size_t n, float* out4);
 void     m17port_limit_iir(const float* in, float* out, size_t n);
+void     m17port_correlate_trace(const float* in, size_t n, float* out5);
 void     m17port_correlator(const float* in, size_t n, uint8_t sample_index, float* corr4, float* mnmx2,
                             float* limit, uint8_t* index);
 void     m17port_clock(const uint8_t* ops, const uint8_t* args, const uint32_t* dt, size_t n,

@@ -285,6 +285,22 @@ void m17ref_correlator(const float* in, size_t n, uint8_t sample_index, float* c
     *index = uint8_t(c.index());
 }
 
+// Correlator.h:43-64 per sample: out5[5 i + 0] = limit() after sample i, [1..4] = correlate() with the four
+// sync words of M17Demodulator.h:154-157, correlator clocked on every sample.
+void m17ref_correlate_trace(const float* in, size_t n, float* out5)
+{
+    Correlator<float> c;
+    c.buffer_.fill(0);
+    for (size_t i = 0; i != n; ++i) {
+        c.sample(in[i]);
+        out5[5 * i + 0] = c.limit();
+        out5[5 * i + 1] = c.correlate({+3,-3,+3,-3,+3,-3,+3,-3});
+        out5[5 * i + 2] = c.correlate({+3,+3,+3,+3,-3,-3,+3,-3});
+        out5[5 * i + 3] = c.correlate({3,-3,3,3,-3,-3,-3,-3});
+        out5[5 * i + 4] = c.correlate({+3,+3,+3,+3,+3,+3,-3,+3});
+    }
+}
+
 // KalmanFilter.h:18-66 + ClockRecovery.h:33-88.  ops[i]: 0 = reset(arg),
 // 1 = update(uint8 arg) after `dt[i]` operator() calls, 2 = update() (dead
 // reckoning) after dt[i] more calls.  out[i] = {sample_index, clock_estimate,

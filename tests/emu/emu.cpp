@@ -12,6 +12,7 @@
 #include "m17b_lane.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -30,9 +31,10 @@ uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p
 struct Emu {
     DevPtrs d{};
     std::vector<uint32_t> st;
-    std::vector<float> ring_y, ring_d, corr_ring, lim_save, sw_samples, fir_snap, seg_ring;
+    std::vector<float> ring_y, ring_d, corr_snap, sw_samples, fir_snap, seg_ring;
+    std::vector<float2> ckpt_ring;
     std::vector<int16_t> llr, ring_x;
-    std::vector<uint32_t> fix_list, dec_list;
+    std::vector<uint32_t> fix_list, dec_list, mask_ring;
     std::vector<uint8_t> dec_bytes;
     std::vector<m17b_frame> recs;
     Counters ctr{};
@@ -40,6 +42,8 @@ struct Emu {
     uint32_t head = 0;
     unsigned long long head64 = 0;
 };
+
+uint32_t g_origin = 0;       // ring position of the first sample (wrap-around tests)
 
 void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
 {
@@ -60,8 +64,9 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.ring_y.assign((size_t) d.ring_lines * np * kLine, 0.f);
     m.ring_d.assign((size_t) d.ring_lines * np * kLine, 0.f);
     m.ring_x.assign((size_t) d.ring_lines * np * kLine, 0);
-    m.corr_ring.assign(kRing * np, 0.f);
-    m.lim_save.assign(8 * np, 0.f);
+    m.corr_snap.assign(80 * np, 0.f);
+    m.mask_ring.assign((size_t) d.ring_lines * np * 4, 0);
+    m.ckpt_ring.assign((size_t) d.ring_lines * np * 4, float2{0.f, 0.f});
     d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
     m.seg_ring.assign((size_t) d.n_seg * 4 * np, 0.f);
     m.fix_list.assign(np, 0);
@@ -71,10 +76,11 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.llr.assign(184 * np, 0);
     m.dec_bytes.assign(56 * np, 0);
     m.recs.resize(d.rec_cap);
-    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_ring = m.corr_ring.data();
-    d.lim_save = m.lim_save.data(); d.seg_ring = m.seg_ring.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
+    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_snap = m.corr_snap.data();
+    d.mask_ring = m.mask_ring.data(); d.ckpt_ring = m.ckpt_ring.data(); d.seg_ring = m.seg_ring.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
-    for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0));
+    for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0), g_origin);
+    m.head = g_origin;
 }
 
 void round(Emu& m, bool defer)
@@ -84,26 +90,33 @@ void round(Emu& m, bool defer)
     m.ctr.deferred = 0;
     m.ctr.fix_count = 0;
     for (int k = 0; k != 5; ++k) m.ctr.dec_count[k] = 0;
-    float ring[kRing], lim[8];
-    for (uint32_t s = 0; s != d.n_streams; ++s) {
-        LaneIo e;
-        e.llr_tab = &m.tab;
-        e.sb = d.st + st_index(s, 0);
-        e.ring = ring; e.lim = lim; e.ring_base = ring; e.lim_base = lim; e.col = 0;
-        e.sw_samples = d.sw_samples + s; e.llr = d.llr + s; e.snap = d.fir_snap + s;
-        e.ring_y = d.ring_y; e.ring_d = d.ring_d; e.ring_x = d.ring_x;
-        e.np = d.np; e.lmask = d.ring_lines - 1; e.s = s;
-        scan_lane(d, e, m.head, m.head64, true, defer);
+    for (uint32_t s = 0; s != d.n_streams; ++s) scan_lane(d, make_io(d, s, &m.tab), m.head, m.head64, true, defer);
+    if (const char* t = getenv("M17EMU_TRACE")) {
+        const uint32_t s = (uint32_t) atoi(t);
+        const uint32_t* sb = d.st + st_index(s, 0);
+        const uint32_t fl = sb[F_FLAGS * 32];
+        fprintf(stderr, "emu s=%u pos=%u state=%u si=%u ssi=%u csi=%u dcd=%u trig=%u sc=%d miss=%d cnt=%u init=%u ckc=%u idx=%u fi=%u gk=%u evm=%.9g off=%.9g idev=%.9g ckest=%.9g h1=%.9g pend=%u fix=%u nr=%u nu=%u\n",
+                s, sb[F_POS * 32], fl & 7, (fl >> FL_SI_SHIFT) & 15, (fl >> FL_SSI_SHIFT) & 15, (fl >> FL_CSI_SHIFT) & 15, !!(fl & FL_DCD), !!(fl & FL_DCD_TRIG),
+                (int) sb[F_SYNC_COUNT * 32], (int) sb[F_MISSING * 32], sb[F_CNT * 32] & 0xFFFF, sb[F_CNT * 32] >> 16, sb[F_CK_COUNT * 32],
+                sb[F_IDX * 32] & 0xFF, (sb[F_IDX * 32] >> 8) & 0xFFFF, sb[F_IDX * 32] >> 24, u2f(sb[F_EVM * 32]), u2f(sb[F_OFFSET * 32]), u2f(sb[F_IDEV * 32]),
+                u2f(sb[F_CK_EST * 32]), u2f(sb[F_IIR0 * 32]), !!(fl & FL_PENDING), !!(fl & FL_FIXUP), !!(fl & FL_NEED_RESET), !!(fl & FL_NEED_UPDATE));
     }
     uint16_t hist[244];
     for (int k = 0; k != 5; ++k)
         for (uint32_t q = 0; q != m.ctr.dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) k * d.np + q], hist, m.head, m.head64);
-    for (uint32_t q = 0; q != m.ctr.fix_count; ++q) fixup_lane(d, m.fix_list[q], m.head);
+    for (uint32_t q = 0; q != m.ctr.fix_count; ++q) {
+        const uint32_t s = m.fix_list[q];
+        fixup_lane(d, s, m.head);
+        search_lane(d, s, m.head);
+        d.st[st_index(s, F_FLAGS)] &= ~FL_FIXUP;
+    }
 }
 
 } // namespace
 
 extern "C" {
+
+void m17emu_set_origin(uint32_t origin) { g_origin = origin; }
 
 // The scan's soft-slicer look-up (llr4, m17b_lane.cuh) for n samples -> packed (second << 8 | first) pairs.
 void m17emu_llr4(const float* samples, size_t n, uint16_t* out)

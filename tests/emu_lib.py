@@ -21,8 +21,9 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
-def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, streaming: bool = False) -> list[np.ndarray]:
+def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, streaming: bool = False, origin: int = 0) -> list[np.ndarray]:
     """Run the emulated scan/decode lanes over [n_streams, n] int16 fed in submits of the given sizes."""
+    lib().m17emu_set_origin(ctypes.c_uint32(origin & 0xFFFFFFFF))
     from m17_cxx_demod_b200.demod import FRAME_DTYPE, split_by_stream
     samples = np.ascontiguousarray(samples, dtype=np.int16)
     ns, n = samples.shape

@@ -315,3 +315,98 @@ def test_cli_bert_bit_error_rate_line(tmp_path):
     assert lines, run.stderr[-400:]
     ber, bits = float(lines[-1][0]), int(lines[-1][1])
     assert 0 < bits <= 197 * n_bert and ber < 0.2
+
+
+def _expected_diagnostics(tr):
+    """The reference's diagnostic callbacks (M17Demodulator.h:675-689,742-752) restated over the oracle's per-sample
+    trace: count_ is reset to 0 exactly on the samples that fire one (after the 1920-sample start-up)."""
+    idx = np.nonzero(tr["count"][1920:] == 0)[0] + 1920
+    was_dcd = tr["dcd"][idx - 1] != 0                     # which branch of operator() the sample took
+    out = np.zeros(len(idx), m.demod.DIAG_REC_DTYPE)
+    t = tr[idx]
+    out["dcd"] = t["dcd"]
+    out["evm"] = np.where(was_dcd, t["evm"], np.float32(0))        # evm.evm() with dcd_, dev.error() == 0 without
+    with np.errstate(divide="ignore", invalid="ignore"):
+        out["deviation"] = np.float32(2400) / t["dev_idev"]        # FreqDevEstimator.h:52
+    out["offset"] = t["dev_offset"]
+    out["locked"] = t["demod_state"] != 0
+    out["clock"] = t["clock_est"]
+    out["sample_index"] = t["sample_index"]; out["sync_index"] = t["sync_sample_index"]; out["clock_index"] = t["clock_sample_index"]
+    out["viterbi_cost"] = t["viterbi_cost"]
+    out["samples"] = idx + 1
+    return out
+
+
+@pytest.mark.parametrize("streaming", [False, True])
+def test_diagnostics_match_oracle_trace(streaming):
+    """Every diagnostic callback the reference would make (every 384 samples without carrier, every 960 with), with
+    its arguments bit for bit: dcd, evm, deviation, offset, locked, clock, the three sample indices, viterbi cost."""
+    x = gen.generate(random_params(31, gen.MIXED, 24), 96000)
+    want_rec, tr = ol.demod_batch("port", x, trace=True)
+    flags = m.demod.DIAG_RECORDS | (m.STREAMING if streaming else 0)
+    with m.Demodulator(24, 9600, flags=flags) as d:
+        got_rec = d.demodulate(x, chunk=9600 if streaming else 7001)
+        diag = d.diag_drain()
+        last = [d.diag(s) for s in range(24)]
+    assert_records_match(want_rec, got_rec, "diag run")
+    fields = ["dcd", "evm", "deviation", "offset", "locked", "clock", "sample_index", "sync_index", "clock_index", "viterbi_cost", "samples"]
+    n_locked = 0
+    for s in range(24):
+        g = diag[diag["stream"] == s]
+        w = _expected_diagnostics(tr[s])
+        assert len(g) == len(w), f"stream {s}: {len(g)} diagnostic records, reference makes {len(w)} callbacks"
+        for f in fields:
+            a, b = g[f], w[f]
+            if a.dtype.kind == "f":
+                a, b = a.view(np.uint32), b.view(np.uint32)
+            bad = np.nonzero(a != b)[0]
+            assert len(bad) == 0, f"stream {s} field {f}: first mismatch at callback {bad[0]} (sample {w['samples'][bad[0]]}): {g[f][bad[0]]} vs {w[f][bad[0]]}"
+        n_locked += int((w["dcd"] != 0).sum())
+        # m17b_diag_get after the flush = the state the next callback would report
+        t = tr[s][-1]
+        assert last[s].dcd == int(t["dcd"]) and last[s].samples == 96000 and last[s].viterbi_cost == int(t["viterbi_cost"])
+        assert np.float32(last[s].offset).view(np.uint32) == t["dev_offset"].view(np.uint32)
+        assert np.float32(last[s].clock).view(np.uint32) == t["clock_est"].view(np.uint32)
+        assert np.float32(last[s].evm).view(np.uint32) == (t["evm"] if t["dcd"] else np.float32(0)).view(np.uint32)
+    assert n_locked > 200
+
+
+def test_correlator_outputs_match_reference():
+    """north_star: correlator outputs within 1e-5 relative.  limit_ and the four sync-word correlations per sample
+    (Correlator.h:43-64), bitwise in the exact filter mode, within 1e-5 of the signal scale in FMA mode."""
+    x = gen.generate(random_params(41, gen.MIXED, 16)[:16], 6000)
+    for p in range(16):
+        x[p] = np.roll(x[p], -min(5000, 300 * p))         # signal from the first samples on for most streams
+    which = "ref" if ol.have_ref() else "port"
+    lib = ol.ref() if which == "ref" else ol.port()
+    fn = getattr(lib, f"m17{which}_correlate_trace")
+    port = ol.port()
+    want_y = np.zeros(x.shape, np.float32); want_c = np.zeros(x.shape + (5,), np.float32)
+    for s in range(x.shape[0]):
+        sc = (x[s].astype(np.float64) / 41067.0).astype(np.float32)
+        port.m17port_fir(sc.ctypes.data_as(ctypes.c_void_p), want_y[s].ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(x.shape[1]))
+        fn(want_y[s].ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(x.shape[1]), want_c[s].ctypes.data_as(ctypes.c_void_p))
+    with m.Demodulator(16, 6000) as d:
+        y, c = d.debug_correlate(x)
+    assert np.array_equal(y.view(np.uint32), want_y.view(np.uint32))
+    assert np.array_equal(c.view(np.uint32), want_c.view(np.uint32)), "correlator outputs must be bit-identical in exact mode"
+    assert np.abs(want_c[..., 1:]).max() > 10 and want_c[..., 0].max() > 0.1
+    with m.Demodulator(16, 6000, flags=m.FIR_FMA) as d:
+        _, cf = d.debug_correlate(x)
+    for k in range(5):
+        scale = np.abs(want_c[..., k]).max()
+        assert np.max(np.abs(cf[..., k] - want_c[..., k])) <= 1e-5 * scale, f"column {k}"
+
+
+@pytest.mark.parametrize("streaming", [False, True])
+def test_ring_positions_wrap_at_2_pow_32(streaming):
+    """Ring positions are 32-bit and wrap after 2^32 samples per stream (24.8 h of real time); a context whose
+    streams start 30,016 samples before the wrap must decode across it exactly like one that starts at 0."""
+    x = gen.generate(random_params(51, gen.MIXED, 40), 96000)
+    want, _ = ol.demod_batch("port", x)
+    with m.Demodulator(40, 9600, flags=m.STREAMING if streaming else 0, debug_origin=2**32 - 30016) as d:
+        got = d.demodulate(x, chunk=9600 if streaming else 4801)
+        c = d.counters()
+    assert c.faults == 0 and c.dropped == 0
+    assert_records_match(want, got, "wrap")
+    assert sum(len(r) for r in want) > 300

@@ -51,6 +51,15 @@ def test_emulated_lanes_streaming_deferral(mode):
         check(want, got, f"streaming mode {mode} chunks {chunks}")
 
 
+def test_emulated_lanes_across_the_32_bit_position_wrap():
+    """Ring positions are uint32: a stream that starts 30,016 samples before 2^32 decodes across the wrap unchanged."""
+    x = gen.generate(random_params(51, gen.MIXED, 12), 96000)
+    want, _ = ol.demod_batch("port", x)
+    for streaming, chunks in ((False, [4801]), (True, [9600])):
+        got = emu_lib.demod(x, chunks, streaming=streaming, origin=2**32 - 30016)
+        check(want, got, f"wrap streaming={streaming}")
+
+
 def test_emulated_lanes_idle_and_zero_inputs():
     rng = np.random.default_rng(3)
     x = np.zeros((4, 30000), np.int16)

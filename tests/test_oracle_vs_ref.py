@@ -64,3 +64,15 @@ def test_reference_cli_binary_matches_library(tmp_path):
     assert len(out) == len(rec[0]) > 10
     for line, r in zip(out, rec[0]):
         assert f"cost={int(r['viterbi_cost'])} " in line and ol.TYPE_NAMES[int(r["type"])] in line
+
+
+def test_correlate_trace_port_equals_reference():
+    """Correlator.h:43-64 per sample (limit_ and the four sync-word correlations): the restatement against the
+    reference's own Correlator class -- the oracle of the GPU correlator tap (test_gpu_parity.py)."""
+    import ctypes
+    rng = np.random.default_rng(5)
+    x = rng.normal(0, 1.5, 4000).astype(np.float32)
+    a = np.zeros((4000, 5), np.float32); b = np.zeros((4000, 5), np.float32)
+    ol.ref().m17ref_correlate_trace(x.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(4000), a.ctypes.data_as(ctypes.c_void_p))
+    ol.port().m17port_correlate_trace(x.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(4000), b.ctypes.data_as(ctypes.c_void_p))
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
