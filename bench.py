@@ -312,9 +312,11 @@ def main():
     fir_ms_per_launch = prof_alone.fir_ms / max(1, prof_alone.fir_launches)
     fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
-    kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "aux": prof.aux_ms}
+    kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "fixup_search": prof.fixup_ms,
+                 "tail": prof.aux_ms}
     ksum = sum(kernel_ms.values()) or 1.0
-    launches = int(prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches)
+    launches = int(prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches +
+                   prof.fixup_launches)
 
     line = {
         "metric": "baseband_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -344,6 +346,8 @@ def main():
         "kernel_share": {k: v / ksum for k, v in kernel_ms.items()},
         "kernel_ms_per_step": {k: v / K for k, v in kernel_ms.items()},
         "gpu_launches": launches,
+        "search": {"requests_per_step": prof.search_requests / K, "samples_per_step": prof.search_samples / K,
+                   "note": "streams in ST_UNLOCKED with the carrier detect on ask for a parallel sync-word search over the samples ahead"},
         "clocks": clocks,
         "frames_by_type": list(ctr.frames), "faults": int(ctr.faults), "dropped": int(ctr.dropped),
     }

@@ -152,6 +152,8 @@ typedef struct m17b_profile {
     double   h2d_ms;     uint64_t h2d_bytes;
     double   d2h_ms;     uint64_t d2h_bytes;
     double   dcd_ms;     uint64_t dcd_launches;                              /* carrier-detect pre-pass          */
+    double   fixup_ms;   uint64_t fixup_launches;                            /* filter fix-up + sync-word search */
+    uint64_t search_requests; uint64_t search_samples;                       /* searches served / samples covered */
 } m17b_profile;
 
 uint32_t    m17b_version(void);

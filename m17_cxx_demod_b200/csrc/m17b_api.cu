@@ -69,7 +69,7 @@ struct m17b_ctx {
 
 namespace {
 
-enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H, CAT_DCD };
+enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H, CAT_DCD, CAT_FIXUP };
 
 int fail(m17b_ctx* c, cudaError_t e, const char* what)
 {
@@ -109,6 +109,7 @@ void ev_collect(m17b_ctx* c)
             case CAT_AUX: c->prof.aux_ms += ms; break;
             case CAT_H2D: c->prof.h2d_ms += ms; break;
             case CAT_DCD: c->prof.dcd_ms += ms; break;
+            case CAT_FIXUP: c->prof.fixup_ms += ms; break;
             default: c->prof.d2h_ms += ms; break;
             }
         }
@@ -129,10 +130,10 @@ int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard = 0)
     launch_decode(c->d, c->head, c->head64, st);
     ev_end(c, st, p);
     c->prof.decode_launches += 1;
-    ev_begin(c, st, CAT_AUX, p);
+    ev_begin(c, st, CAT_FIXUP, p);
     launch_fixup(c->d, c->head, c->sm_count, st);
     ev_end(c, st, p);
-    c->prof.aux_launches += 1;
+    c->prof.fixup_launches += 3;
     CK(cudaGetLastError());
     return M17B_OK;
 }
@@ -613,7 +614,13 @@ int m17b_get_profile(m17b_ctx* c, m17b_profile* out, int reset)
     int rc = m17b_sync(c);
     if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
     *out = c->prof;
-    if (reset) c->prof = m17b_profile{};
+    out->search_requests = c->host_ctr.search_requests - c->prof.search_requests;    // prof.* hold the values at the last reset
+    out->search_samples = c->host_ctr.search_samples - c->prof.search_samples;
+    if (reset) {
+        c->prof = m17b_profile{};
+        c->prof.search_requests = c->host_ctr.search_requests;
+        c->prof.search_samples = c->host_ctr.search_samples;
+    }
     return M17B_OK;
 }
 

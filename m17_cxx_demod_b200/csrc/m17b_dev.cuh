@@ -108,6 +108,8 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned int diag_count;      // diagnostic-record cursor (M17B_DIAG_RECORDS), monotonic like rec_count
     unsigned int pad0;
     unsigned long long diag_dropped;
+    unsigned long long search_requests;   // sync-word searches served by search_mask_kernel
+    unsigned long long search_samples;    // ... and the samples they covered
 };
 
 struct DevPtrs {

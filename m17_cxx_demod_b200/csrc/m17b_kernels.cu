@@ -342,123 +342,177 @@ decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
     decode_lane(d, s, hist + threadIdx.x, head, head64);
 }
 
-// What a stream asks for when it cannot go on alone (FL_FIXUP), one CTA per request:
-// (1) Matched-filter fix-up after a carrier-detect gap (M17Demodulator.h:675-689: the filter is not
-//     clocked while !dcd_, so its first 149 outputs after it resumes see stale history; fir_kernel
-//     computed them for contiguous history).  Thread k recomputes output k in the reference's tap order
-//     from the snapshot and the scaled inputs staged in shared memory.
-// (2) The sync-word search of a stream in ST_UNLOCKED with the carrier detect on (search_lane in
-//     m17b_lane.cuh is the serial statement of the same pass): do_unlocked() evaluates up to two
-//     correlations and their thresholds on EVERY sample (M17Demodulator.h:288-342).  That is feed-forward
-//     once limit_ is known, so per tile of 512 samples one thread runs the limit biquad (the only
-//     recurrence, ~12 dependent cycles per sample) and then every thread takes samples: three 8-tap
-//     correlations from the staged filter outputs and SyncWord::triggered's comparison.  The stream then
-//     jumps from trigger to trigger through the masks (scan_lane's search walk) and adopts the limit-filter
-//     history left at the block ends.
-constexpr int kFixThreads = 256;
-constexpr int kSearchTile = 512;
+// What a stream asks for when it cannot go on alone (FL_FIXUP), three launches per round:
+//
+// fixup_kernel (one CTA per request): matched-filter fix-up after a carrier-detect gap
+//     (M17Demodulator.h:675-689: the filter is not clocked while !dcd_, so its first 149 outputs after it
+//     resumes see stale history; fir_kernel computed them for contiguous history).  Thread k recomputes
+//     output k in the reference's tap order from the snapshot and the scaled inputs staged in shared memory.
+//
+// The sync-word search of a stream in ST_UNLOCKED with the carrier detect on (search_lane in m17b_lane.cuh is
+// the serial statement of the same pass): do_unlocked() evaluates up to two correlations and their thresholds
+// on EVERY sample (M17Demodulator.h:288-342).  That is feed-forward once limit_ is known, so it is split into
+// search_limit_kernel (one thread per request): the limit biquad over [F_POS, head), the only recurrence
+//     (~12 dependent cycles per sample), leaving its history at every block end (ckpt_ring), and
+// search_mask_kernel (one thread per request and 8-sample block): limit_ for the block's samples from the
+//     block before's history, three 8-tap correlations per sample straight from the sample ring and
+//     SyncWord::triggered's comparison -> one mask word per block.
+// The stream then jumps from trigger to trigger through the masks (scan_lane's search walk) and adopts the
+// limit-filter history where it leaves the search.
+constexpr int kFixThreads = 160;
 
 __global__ void __launch_bounds__(kFixThreads)
 fixup_kernel(DevPtrs d, uint32_t head)
 {
     __shared__ float xs[kTapsUsed], snap[kTapsUsed];
-    __shared__ float ys[70 + kSearchTile];                 // filter outputs of [t0 - 70, t0 + tile) as the correlator saw them
-    __shared__ float lim[kSearchTile];                     // limit_ after each sample of the tile
-    __shared__ uint8_t tbits[kSearchTile];                 // trigger bits of each sample
     const uint32_t n_req = d.ctr->fix_count;
     const uint32_t cmask = d.ring_lines - 1;
     const int t = threadIdx.x;
     for (uint32_t q = blockIdx.x; q < n_req; q += gridDim.x) {
         const uint32_t s = d.fix_list[q];
         uint32_t* sb = d.st + st_index(s, 0);
-        // ---- (1) filter outputs after the resume position R ----
         const uint32_t R = sb[F_GAPR * 32];
         const int done = (int) sb[F_GAPDONE * 32];
         const uint32_t avail = head - R;
         const int upto = avail < (uint32_t) kTapsUsed ? (int) avail : kTapsUsed;
-        if (done < upto) {                                  // CTA-uniform
-            if (t < kTapsUsed) {
-                snap[t] = d.fir_snap[(size_t) t * d.np + s];
-                xs[t] = t < upto ? scale_i16(d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)]) : 0.f;
-            }
-            __syncthreads();
-            if (t >= done && t < upto) {
-                float result = 0.0f;
-                for (int i = 0; i != kTapsUsed; ++i) {
-                    float v = i <= t ? xs[t - i] : snap[i - t - 1];
-                    result = __fadd_rn(result, __fmul_rn(v, c_tab.taps[i]));
-                }
-                d.ring_y[ring_off(R + (uint32_t) t, cmask, d.np, s)] = result;
-            }
-            __syncthreads();                                // the corrected outputs are read below
-        }
-        // ---- (2) sync-word search over [F_POS, head) ----
-        if (wants_search(sb, head)) {                       // CTA-uniform
-            const uint32_t from = sb[F_POS * 32];
-            const int k0 = (int) (sb[F_IDX * 32] >> 24);    // samples clocked since the last resume, before `from`
-            const bool gap = k0 < kTapsUsed;                // ... which is then at Rk = from - k0; older samples are the snapshot's
-            const uint32_t Rk = from - (uint32_t) k0;
-            Biquad b;
-            b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
-            for (uint32_t t0 = from & ~7u; (int32_t) (head - t0) > 0; t0 += kSearchTile) {
-                const uint32_t left = head - t0;
-                const int n = left < (uint32_t) kSearchTile ? (int) left : kSearchTile;
-                for (int i = t; i < 70 + n; i += kFixThreads) {
-                    const uint32_t v = t0 - 70u + (uint32_t) i;
-                    float y;
-                    if (gap && (int32_t) (v - Rk) < 0) {
-                        const int idx = 79 - (int) (Rk - 1u - v);
-                        y = idx >= 0 ? d.corr_snap[(size_t) idx * d.np + s] : 0.f;     // idx < 0: never used (older than 70 before `from`)
-                    } else {
-                        y = d.ring_y[ring_off(v, cmask, d.np, s)];
-                    }
-                    ys[i] = y;
-                }
-                __syncthreads();
-                if (t == 0) {
-                    for (int i = 0; i != n; ++i) {
-                        const uint32_t p = t0 + (uint32_t) i;
-                        if ((int32_t) (p - from) < 0) continue;
-                        lim[i] = limit_step(b, ys[70 + i]);
-                        if ((p & 7u) == 7u) d.ckpt_ring[blk_off(p, cmask, d.np, s)] = make_float2(b.h1, b.h2);
-                    }
-                }
-                __syncthreads();
-                for (int i = t; i < kSearchTile; i += kFixThreads) {
-                    uint32_t bits = 0;
-                    if (i < n && (int32_t) (t0 + (uint32_t) i - from) >= 0) {
-                        float y8[8];
-#pragma unroll
-                        for (int j = 0; j != 8; ++j) y8[j] = ys[i + 10 * j];       // samples 70, 60, ..., 0 steps back
-                        bits = trigger_bits(lim[i], corr8(y8, kWordPreamble), corr8(y8, kWordLsf), corr8(y8, kWordPacket), 0.f);
-                    }
-                    tbits[i] = (uint8_t) bits;
-                }
-                __syncthreads();
-                if (t < (n + 7) / 8) {
-                    uint32_t word = 0;
-#pragma unroll
-                    for (int j = 0; j != 8; ++j) {
-                        const uint32_t bits = tbits[8 * t + j];
-                        word |= ((bits & 1u) << j) | (((bits >> 1) & 1u) << (8 + j)) | (((bits >> 2) & 1u) << (16 + j));
-                    }
-                    d.mask_ring[blk_off(t0 + 8u * (uint32_t) t, cmask, d.np, s)] = word;
-                }
-                __syncthreads();
-            }
-        }
-        if (t == 0) {
-            if (done < upto) sb[F_GAPDONE * 32] = (uint32_t) upto;
-            if (wants_search(sb, head)) { sb[F_SFROM * 32] = sb[F_POS * 32]; sb[F_STO * 32] = head; }
-            sb[F_FLAGS * 32] &= ~FL_FIXUP;
+        if (done >= upto) continue;                         // CTA-uniform
+        if (t < kTapsUsed) {
+            snap[t] = d.fir_snap[(size_t) t * d.np + s];
+            xs[t] = t < upto ? scale_i16(d.ring_x[ring_off(R + (uint32_t) t, cmask, d.np, s)]) : 0.f;
         }
         __syncthreads();
+        if (t >= done && t < upto) {
+            float result = 0.0f;
+            for (int i = 0; i != kTapsUsed; ++i) {
+                float v = i <= t ? xs[t - i] : snap[i - t - 1];
+                result = __fadd_rn(result, __fmul_rn(v, c_tab.taps[i]));
+            }
+            d.ring_y[ring_off(R + (uint32_t) t, cmask, d.np, s)] = result;
+        }
+        __syncthreads();
+        if (t == 0) sb[F_GAPDONE * 32] = (uint32_t) upto;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+search_limit_kernel(DevPtrs d, uint32_t head)
+{
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= d.ctr->fix_count) return;
+    const uint32_t s = d.fix_list[q];
+    const uint32_t* sb = d.st + st_index(s, 0);
+    if (!wants_search(sb, head)) return;
+    const uint32_t lmask = d.ring_lines - 1;
+    const uint32_t from = sb[F_POS * 32];
+    Biquad b;
+    b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
+    // blocks from the one that contains `from`; the next block's samples are requested a block of arithmetic ahead
+    // and the ring line after that is pulled into L2
+    uint32_t base = from & ~7u;
+    const float4* py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base, lmask, d.np, s));
+    float4 a0 = py[0], a1 = py[1];
+    for (; (int32_t) (head - base) > 0; base += 8u) {
+        const float y[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base + 8u, lmask, d.np, s));
+        a0 = py[0]; a1 = py[1];
+        if ((base & 31u) == 0u)
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(d.ring_y + ring_off(base + 96u, lmask, d.np, s)));
+        const uint32_t left = head - base;
+        if ((int32_t) (base - from) >= 0 && left >= 8u) {
+#pragma unroll
+            for (int j = 0; j != 8; ++j) limit_step(b, y[j]);
+            d.ckpt_ring[blk_off(base, lmask, d.np, s)] = make_float2(b.h1, b.h2);
+        } else {
+#pragma unroll
+            for (int j = 0; j != 8; ++j)
+                if ((int32_t) (base + (uint32_t) j - from) >= 0 && (uint32_t) j < left) limit_step(b, y[j]);
+            if (left >= 8u) d.ckpt_ring[blk_off(base, lmask, d.np, s)] = make_float2(b.h1, b.h2);
+        }
+    }
+}
+
+constexpr int kMaskThreads = 128;
+
+__global__ void __launch_bounds__(kMaskThreads)
+search_mask_kernel(DevPtrs d, uint32_t head)
+{
+    const uint32_t n_req = d.ctr->fix_count;
+    const uint32_t lmask = d.ring_lines - 1;
+    for (uint32_t q = blockIdx.y; q < n_req; q += gridDim.y) {
+        const uint32_t s = d.fix_list[q];
+        uint32_t* sb = d.st + st_index(s, 0);
+        const bool search = wants_search(sb, head);                 // CTA-uniform
+        const bool first = blockIdx.x == 0 && threadIdx.x == 0;
+        if (search) {
+            const uint32_t from = sb[F_POS * 32];
+            const int k0 = (int) (sb[F_IDX * 32] >> 24);            // samples clocked since the last resume, before `from`
+            const bool gap = k0 < kTapsUsed;                        // ... which is then at Rk = from - k0; older samples are the snapshot's
+            const uint32_t Rk = from - (uint32_t) k0;
+            const uint32_t base0 = from & ~7u;
+            const uint32_t n_blk = (head - base0 + 7u) >> 3;
+            for (uint32_t bi = blockIdx.x * kMaskThreads + threadIdx.x; bi < n_blk; bi += gridDim.x * kMaskThreads) {
+                const uint32_t base = base0 + 8u * bi;
+                Biquad b;
+                if (bi == 0) { b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]); }
+                else { const float2 c = d.ckpt_ring[blk_off(base - 8u, lmask, d.np, s)]; b.h1 = c.x; b.h2 = c.y; }
+                // the filter outputs the block's correlations touch: 8 runs of 8 consecutive samples, 10 apart
+                float w[8][8];
+                if (!gap || (int32_t) (base - 70u - Rk) >= 0) {
+#pragma unroll
+                    for (int i = 0; i != 8; ++i) {
+                        const uint32_t v = base - 70u + 10u * (uint32_t) i;        // even: the run is 4 aligned pairs
+#pragma unroll
+                        for (int j = 0; j != 8; j += 2) {
+                            const float2 t2 = *reinterpret_cast<const float2*>(d.ring_y + ring_off(v + (uint32_t) j, lmask, d.np, s));
+                            w[i][j] = t2.x; w[i][j + 1] = t2.y;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i != 8; ++i)
+#pragma unroll
+                        for (int j = 0; j != 8; ++j) {
+                            const uint32_t v = base - 70u + 10u * (uint32_t) i + (uint32_t) j;
+                            float y;
+                            if ((int32_t) (v - Rk) < 0) {
+                                const int idx = 79 - (int) (Rk - 1u - v);
+                                y = idx >= 0 ? d.corr_snap[(size_t) idx * d.np + s] : 0.f;   // idx < 0: older than 70 before `from`, never used
+                            } else {
+                                y = d.ring_y[ring_off(v, lmask, d.np, s)];
+                            }
+                            w[i][j] = y;
+                        }
+                }
+                uint32_t word = 0;
+#pragma unroll
+                for (int j = 0; j != 8; ++j) {
+                    const uint32_t p = base + (uint32_t) j;
+                    if ((int32_t) (p - from) < 0 || (int32_t) (head - p) <= 0) continue;
+                    const float limit = limit_step(b, w[7][j]);
+                    const float y8[8] = {w[0][j], w[1][j], w[2][j], w[3][j], w[4][j], w[5][j], w[6][j], w[7][j]};
+                    const uint32_t bits = trigger_bits(limit, corr8(y8, kWordPreamble), corr8(y8, kWordLsf), corr8(y8, kWordPacket), 0.f);
+                    word |= ((bits & 1u) << j) | (((bits >> 1) & 1u) << (8 + j)) | (((bits >> 2) & 1u) << (16 + j));
+                }
+                d.mask_ring[blk_off(base, lmask, d.np, s)] = word;
+            }
+        }
+        if (first) {
+            if (search) {
+                sb[F_SFROM * 32] = sb[F_POS * 32]; sb[F_STO * 32] = head;
+                atomicAdd(&d.ctr->search_requests, 1ull);
+                atomicAdd(&d.ctr->search_samples, (unsigned long long) (head - sb[F_POS * 32]));
+            }
+            sb[F_FLAGS * 32] &= ~FL_FIXUP;
+        }
     }
 }
 
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
 {
     fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head);
+    search_limit_kernel<<<d.np / 128, 128, 0, s>>>(d, head);
+    // a request's span is at most the ring: x = its blocks in strides of the grid, y = requests in strides of the grid
+    search_mask_kernel<<<dim3(8, (unsigned) sm_count * 2), kMaskThreads, 0, s>>>(d, head);
 }
 
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)

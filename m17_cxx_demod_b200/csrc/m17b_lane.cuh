@@ -863,6 +863,19 @@ M17B_FN void load_chunk(Chunk& c, const LaneIo& e, uint32_t base)
     c.y[0] = a0.x; c.y[1] = a0.y; c.y[2] = a0.z; c.y[3] = a0.w; c.y[4] = a1.x; c.y[5] = a1.y; c.y[6] = a1.z; c.y[7] = a1.w;
 }
 
+// the limit filter over block samples [jb, je)
+M17B_FN void bq_feed(Biquad& b, const float (&y)[8], int jb, int je)
+{
+    if (jb == 0 && je == 8) {
+#pragma unroll
+        for (int i = 0; i != 8; ++i) limit_step(b, y[i]);
+    } else {
+#pragma unroll
+        for (int i = 0; i != 8; ++i)
+            if (i >= jb && i < je) limit_step(b, y[i]);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // Carrier-detect pre-pass.  DataCarrierDetect::operator() (DataCarrierDetect.h:53-58) clocks the two-bin
 // sliding DFT (SlidingDFT.h:118-132) on EVERY input sample, whatever the demodulator state, and sums
@@ -1195,6 +1208,116 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
             pos = pos0 + (uint32_t) j;
             z.count += j;
             bq_catch_up(z, e, pos0, pos);
+            if (z.count == 960) {                           // :742-752
+                float l1, l2;
+                dcd_sums(d, e, pos, head, head64, 960, l1, l2);
+                update_dcd(z, e);
+                z.count = 0;
+                emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), true);
+                dcd_update(z, l1, l2);
+                if (!z.dcd) gate_off(d, e, z.gap_k, pos);
+            }
+            continue;
+        }
+
+        if (!z.init && z.state == ST_FRAME && !z.need_reset && !z.need_update && z.gap_k >= kTapsUsed) {
+            // ---- frame walk: ST_FRAME, M17Demodulator.h:595-654 ---------------------------------
+            // Inside a frame only two kinds of sample do anything: the one half a symbol away from the symbol
+            // instant (dead-reckoning clock update, which may move sample_index by one) and the symbol instant
+            // itself (slice, soft bits, framer).  The walk goes from event to event by position -- one pass of
+            // the loop = at most one clock update followed by at most one symbol, the order they come in once a
+            // frame is under way, so the lanes of a warp run the same code whatever their symbol phases -- and
+            // feeds the limit filter, which no frame event looks at, whole blocks at a time behind the walk.
+            if (defer && head - pos < 1920u &&
+                frame_end_offset(z.si, z.i10, z.framer_index) - kDeferMarginFrame >= (int) (head - pos)) {
+                deferred = true;                            // this frame ends after the head: the next submit's
+                break;
+            }
+            const uint32_t pos0 = pos;
+            const uint32_t left = head - pos;
+            const int n = (uint32_t) (960 - z.count) < left ? 960 - z.count : (int) left;
+            uint32_t bqp = pos0;                            // the limit filter has consumed [pos0, bqp)
+            Chunk pfa, pfb;                                 // the blocks at bqp & ~7 and after it
+            load_chunk(pfa, e, bqp & ~7u);
+            load_chunk(pfb, e, (bqp & ~7u) + 8u);
+            int done = 0, i10 = z.i10, si = z.si;
+            for (;;) {
+                int dd = si - i10; dd = dd < 0 ? dd + 10 : dd;                  // samples until index() == sample_index
+                int aa = dd >= 5 ? dd - 5 : dd + 5;                             // ... until |sample_index - index()| == 5
+                float ys = e.ring_y[ring_off(pos0 + (uint32_t) (done + dd), e.lmask, e.np, e.s)];   // requested early
+                if (aa < dd) {
+                    if (aa >= n - done) { z.ck_count += (uint32_t) (n - done); i10 = (i10 + (n - done)) % 10; done = n; break; }
+                    done += aa + 1;
+                    z.ck_count += (uint32_t) (aa + 1);      // clock_recovery(filtered_sample) on every sample, :712
+                    // ClockRecovery.h:76-88 (see do_frame)
+                    const float v = z.ck_sest + z.ck_est * (float) z.ck_count;
+                    const float av = fabsf(v);
+                    float csw;
+                    if (av < 10.f) csw = v;
+                    else if (av < 20.f) csw = v - (v < 0 ? -10.0f : 10.0f);
+                    else csw = (float) fmod((double) v, 10.0);
+                    int r;
+                    if (csw < 0.f) r = (int) (int8_t) round((double) csw + 10.0);
+                    else r = round_half_away(csw);
+                    const int nsi = wrap_index(r);
+                    i10 = si >= 4 ? si - 4 : si + 6;        // index() of the sample after the one at (si + 5) % 10
+                    z.csi = nsi;
+                    if (nsi != si) {
+                        si = nsi;
+                        dd = si - i10; dd = dd < 0 ? dd + 10 : dd;
+                        ys = e.ring_y[ring_off(pos0 + (uint32_t) (done + dd), e.lmask, e.np, e.s)];
+                    } else {
+                        dd = 4;                             // from (si + 6) % 10 to si
+                    }
+                    aa = dd >= 5 ? dd - 5 : dd + 5;
+                }
+                if (aa >= dd) {
+                    if (dd >= n - done) { z.ck_count += (uint32_t) (n - done); i10 = (i10 + (n - done)) % 10; done = n; break; }
+                    done += dd + 1;
+                    z.ck_count += (uint32_t) (dd + 1);
+                    i10 = si == 9 ? 0 : si + 1;
+                    float sample = ys - z.offset;
+                    sample *= z.idev;                       // polarity is +1 and never changes
+                    // SymbolEvm.h:31-51 + StandardDeviation.h:68-72
+                    float err;
+                    if (sample > 2) err = sample - 3;
+                    else if (sample > 0) err = sample - 1;
+                    else if (sample > -2) err = sample + 1;
+                    else err = sample + 3;
+                    const float alpha = (float) (1.0 / 184);
+                    z.evm -= z.evm * alpha;
+                    z.evm += (err * err) * alpha;
+                    const uint32_t pair = llr4(*e.llr_tab, sample);
+                    e.llr[(size_t) (z.framer_index >> 1) * e.np] = (int16_t) pair;      // M17Framer.h:42-53
+                    z.framer_index += 2;
+                    if (z.framer_index == 368) {
+                        z.framer_index = 0;
+                        z.sync_count = 0;
+                        z.pending = true;                   // decoder(...) runs in decode_kernel
+                        z.state = ST_TBD;
+                        break;
+                    }
+                }
+                // the limit filter takes the whole blocks behind the walk
+                while (((bqp & ~7u) + 8u) - pos0 <= (uint32_t) done) {
+                    bq_feed(z.bq, pfa.y, (int) (bqp & 7u), 8);
+                    bqp = (bqp & ~7u) + 8u;
+                    pfa = pfb;
+                    load_chunk(pfb, e, bqp + 8u);
+                }
+            }
+            pos = pos0 + (uint32_t) done;
+            while (((bqp & ~7u) + 8u) - pos0 <= (uint32_t) done) {
+                bq_feed(z.bq, pfa.y, (int) (bqp & 7u), 8);
+                bqp = (bqp & ~7u) + 8u;
+                pfa = pfb;
+                load_chunk(pfb, e, bqp + 8u);
+            }
+            if (bqp != pos) bq_feed(z.bq, pfa.y, (int) (bqp & 7u), (int) (pos - (bqp & ~7u)));
+            z.si = si;
+            z.i10 = i10;
+            z.corr_pos = (z.corr_pos + done) % 80;
+            z.count += done;
             if (z.count == 960) {                           // :742-752
                 float l1, l2;
                 dcd_sums(d, e, pos, head, head64, 960, l1, l2);

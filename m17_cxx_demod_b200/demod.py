@@ -54,7 +54,9 @@ class Profile(ctypes.Structure):
                 ("aux_ms", ctypes.c_double), ("aux_launches", ctypes.c_uint64),
                 ("h2d_ms", ctypes.c_double), ("h2d_bytes", ctypes.c_uint64),
                 ("d2h_ms", ctypes.c_double), ("d2h_bytes", ctypes.c_uint64),
-                ("dcd_ms", ctypes.c_double), ("dcd_launches", ctypes.c_uint64)]
+                ("dcd_ms", ctypes.c_double), ("dcd_launches", ctypes.c_uint64),
+                ("fixup_ms", ctypes.c_double), ("fixup_launches", ctypes.c_uint64),
+                ("search_requests", ctypes.c_uint64), ("search_samples", ctypes.c_uint64)]
 
 
 _lib = None

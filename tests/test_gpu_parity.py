@@ -345,8 +345,14 @@ def test_diagnostics_match_oracle_trace(streaming):
     want_rec, tr = ol.demod_batch("port", x, trace=True)
     flags = m.demod.DIAG_RECORDS | (m.STREAMING if streaming else 0)
     with m.Demodulator(24, 9600, flags=flags) as d:
-        got_rec = d.demodulate(x, chunk=9600 if streaming else 7001)
-        diag = d.diag_drain()
+        chunk = 9600 if streaming else 7001
+        recs, diags = [], []
+        for o in range(0, x.shape[1], chunk):              # the facade's pattern: frames, then diagnostics, per block
+            d.submit(np.ascontiguousarray(x[:, o:o + chunk]))
+            recs.append(d.drain())
+            diags.append(d.diag_drain())
+        got_rec = m.demod.split_by_stream(np.concatenate(recs), 24)
+        diag = np.concatenate(diags)
         last = [d.diag(s) for s in range(24)]
     assert_records_match(want_rec, got_rec, "diag run")
     fields = ["dcd", "evm", "deviation", "offset", "locked", "clock", "sample_index", "sync_index", "clock_index", "viterbi_cost", "samples"]
