@@ -83,7 +83,7 @@ struct M17Demodulator
         cfg.n_streams = 1;
         cfg.device = device;
         cfg.max_chunk = uint32_t(block_);
-        cfg.flags = flags;
+        cfg.flags = flags | M17B_DIAG_RECORDS;      // the diagnostic callback fires at the reference cadence
         int rc = m17b_create(&cfg, &ctx_);
         if (rc != M17B_OK) throw std::runtime_error(std::string("m17b_create: ") + m17b_strerror(rc));
         pending_.reserve(block_);
@@ -112,33 +112,53 @@ struct M17Demodulator
         if (pending_.size() == block_) flush();
     }
 
-    /// Demodulate everything buffered so far and fire the callbacks.
+    /// Demodulate everything buffered so far and fire the callbacks in the reference's order: a frame callback
+    /// fires on the sample that completes the frame (M17Demodulator.h:646), the diagnostic callback every 384
+    /// samples without carrier (:675-689) and every 960 with (:742-752), after the frame callback of the same sample.
     void flush()
     {
         if (!pending_.empty()) {
             int rc = m17b_submit(ctx_, pending_.data(), pending_.size(), pending_.size(), M17B_HOST);
             if (rc != M17B_OK) throw std::runtime_error(std::string("m17b_submit: ") + m17b_strerror(rc));
+            submitted_ = true;      // the buffer must stay valid until the drain below; it is released right after it
         }
-        m17b_frame frames[64];
+        frames_.clear();
+        diags_.clear();
         size_t n = 0;
+        int rc_drain = M17B_OK;
         do {
-            int rc = m17b_drain(ctx_, frames, 64, &n);
-            if (rc != M17B_OK) throw std::runtime_error(std::string("m17b_drain: ") + m17b_strerror(rc) + " " + m17b_last_cuda_error(ctx_));
-            for (size_t i = 0; i != n; ++i) {
+            const size_t at = frames_.size();
+            frames_.resize(at + 256);
+            rc_drain = m17b_drain(ctx_, frames_.data() + at, 256, &n);
+            frames_.resize(at + (rc_drain == M17B_OK || rc_drain == M17B_EOVERFLOW ? n : 0));
+        } while ((rc_drain == M17B_OK || rc_drain == M17B_EOVERFLOW) && n == 256);
+        if (submitted_) { pending_.clear(); submitted_ = false; }     // consumed whatever the drain says: never resubmitted
+        if (rc_drain != M17B_OK)
+            throw std::runtime_error(std::string("m17b_drain: ") + m17b_strerror(rc_drain) + " " + m17b_last_cuda_error(ctx_));
+        do {
+            const size_t at = diags_.size();
+            diags_.resize(at + 256);
+            int rc = m17b_diag_drain(ctx_, diags_.data() + at, 256, &n);
+            diags_.resize(at + (rc == M17B_OK ? n : 0));
+            if (rc != M17B_OK) throw std::runtime_error(std::string("m17b_diag_drain: ") + m17b_strerror(rc));
+        } while (n == 256);
+        size_t fi = 0, di = 0;
+        while (fi != frames_.size() || di != diags_.size()) {
+            // the frame callback of sample p (0-based) precedes the diagnostic callback fired after p + 1 samples
+            if (fi != frames_.size() && (di == diags_.size() || frames_[fi].sample_pos < diags_[di].d.samples)) {
+                const m17b_frame& f = frames_[fi++];
                 M17FrameDecoder::output_buffer_t out;
-                out.type = M17FrameDecoder::FrameType(frames[i].type);
-                std::memcpy(out.packet.data(), frames[i].payload, 26);
-                std::memcpy(out.lsf.data(), frames[i].lsf, 30);
-                if (callback_) callback_(out, frames[i].viterbi_cost);
+                out.type = M17FrameDecoder::FrameType(f.type);
+                std::memcpy(out.packet.data(), f.payload, 26);
+                std::memcpy(out.lsf.data(), f.lsf, 30);
+                if (callback_) callback_(out, f.viterbi_cost);
+            } else {
+                const m17b_diag& d = diags_[di++].d;
+                dcd_ = d.dcd;
+                if (diagnostic_callback)
+                    diagnostic_callback(d.dcd, FloatType(d.evm), FloatType(d.deviation), FloatType(d.offset), d.locked,
+                                        FloatType(d.clock), d.sample_index, d.sync_index, d.clock_index, d.viterbi_cost);
             }
-        } while (n == 64);
-        pending_.clear();
-        m17b_diag d{};
-        if (m17b_diag_get(ctx_, 0, &d) == M17B_OK) {
-            dcd_ = d.dcd;
-            if (diagnostic_callback)
-                diagnostic_callback(d.dcd, FloatType(d.evm), FloatType(d.deviation), FloatType(d.offset), d.locked,
-                                    FloatType(d.clock), d.sample_index, d.sync_index, d.clock_index, d.viterbi_cost);
         }
     }
 
@@ -149,6 +169,9 @@ private:
     size_t block_;
     m17b_ctx* ctx_ = nullptr;
     std::vector<int16_t> pending_;
+    std::vector<m17b_frame> frames_;
+    std::vector<m17b_diag_rec> diags_;
+    bool submitted_ = false;
     bool dcd_ = false;
     bool passall_ = false;
 };

@@ -380,9 +380,10 @@ def test_diagnostics_match_oracle_trace(streaming):
 def test_correlator_outputs_match_reference():
     """north_star: correlator outputs within 1e-5 relative.  limit_ and the four sync-word correlations per sample
     (Correlator.h:43-64), bitwise in the exact filter mode, within 1e-5 of the signal scale in FMA mode."""
-    x = gen.generate(random_params(41, gen.MIXED, 16)[:16], 6000)
-    for p in range(16):
-        x[p] = np.roll(x[p], -min(5000, 300 * p))         # signal from the first samples on for most streams
+    # transmissions that start within the first 600 samples: preamble, LSF and the first frames inside the 9000 samples
+    x = gen.generate([gen.default_params(seed=4100 + p, mode=(gen.STREAM, gen.PACKET, gen.BERT)[p % 3], snr_db=4.0 + 2 * p,
+                                         skew_ppm=(p - 8) * 50.0, dc_offset=(p - 8) * 40.0, lead_in=40 * p, tail=0, n_frames=2, repeat=1)
+                      for p in range(16)], 9000)
     which = "ref" if ol.have_ref() else "port"
     lib = ol.ref() if which == "ref" else ol.port()
     fn = getattr(lib, f"m17{which}_correlate_trace")
@@ -392,12 +393,12 @@ def test_correlator_outputs_match_reference():
         sc = (x[s].astype(np.float64) / 41067.0).astype(np.float32)
         port.m17port_fir(sc.ctypes.data_as(ctypes.c_void_p), want_y[s].ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(x.shape[1]))
         fn(want_y[s].ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(x.shape[1]), want_c[s].ctypes.data_as(ctypes.c_void_p))
-    with m.Demodulator(16, 6000) as d:
+    with m.Demodulator(16, 9000) as d:
         y, c = d.debug_correlate(x)
     assert np.array_equal(y.view(np.uint32), want_y.view(np.uint32))
     assert np.array_equal(c.view(np.uint32), want_c.view(np.uint32)), "correlator outputs must be bit-identical in exact mode"
     assert np.abs(want_c[..., 1:]).max() > 10 and want_c[..., 0].max() > 0.1
-    with m.Demodulator(16, 6000, flags=m.FIR_FMA) as d:
+    with m.Demodulator(16, 9000, flags=m.FIR_FMA) as d:
         _, cf = d.debug_correlate(x)
     for k in range(5):
         scale = np.abs(want_c[..., k]).max()
