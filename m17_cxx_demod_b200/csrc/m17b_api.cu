@@ -121,11 +121,12 @@ void ev_collect(m17b_ctx* c)
 int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard = 0)
 {
     EvPair p{};
-    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 8 * sizeof(unsigned int), st));      // lagging, fix_count, dec_count[5], deferred
+    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 10 * sizeof(unsigned int), st));     // lagging, fix_count, dec_count[5], deferred, scan_count[2]
     ev_begin(c, st, CAT_SCAN, p);
+    launch_classify(c->d, c->head, st);
     launch_scan(c->d, c->head, c->head64, defer, guard, st);
     ev_end(c, st, p);
-    c->prof.scan_launches += 1;
+    c->prof.scan_launches += 3;
     ev_begin(c, st, CAT_DECODE, p);
     launch_decode(c->d, c->head, c->head64, st);
     ev_end(c, st, p);
@@ -194,7 +195,7 @@ void free_all(m17b_ctx* c)
     for (auto& e : c->done) if (e) cudaEventDestroy(e);
     if (c->snap) cudaFreeHost(c->snap);
     cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.mask_ring); cudaFree(c->d.ckpt_ring);
-    cudaFree(c->d.corr_snap); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.dec_list); cudaFree(c->d.diag_recs);
+    cudaFree(c->d.corr_snap); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.scan_list); cudaFree(c->d.dec_list); cudaFree(c->d.diag_recs);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr);
     if (c->ready) cudaFreeHost(c->ready);
@@ -309,6 +310,7 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.seg_ring, (size_t) d.n_seg * 4 * np * sizeof(float)));
         CK(cudaMemsetAsync(d.seg_ring, 0, (size_t) d.n_seg * 4 * np * sizeof(float), c->compute));
         CK(cudaMalloc(&d.fix_list, np * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.scan_list, 2 * np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.dec_list, 5 * np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
         CK(cudaMalloc(&d.fir_snap, (size_t) kTapsUsed * np * sizeof(float)));

@@ -105,8 +105,8 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
     unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
     unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
+    unsigned int scan_count[2];   // entries in scan_list per walk class (reset likewise)
     unsigned int diag_count;      // diagnostic-record cursor (M17B_DIAG_RECORDS), monotonic like rec_count
-    unsigned int pad0;
     unsigned long long diag_dropped;
     unsigned long long search_requests;   // sync-word searches served by search_mask_kernel
     unsigned long long search_samples;    // ... and the samples they covered
@@ -122,6 +122,8 @@ struct DevPtrs {
     float* seg_ring;              // [n_seg][4][Np] carrier-detect energy sums per window start (see dcd_lane)
     float2* ckpt_ring;            // [RL][Np][4] limit-filter history after every 8-sample block of a searched span
     uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
+    uint32_t* scan_list;          // [2][Np] streams with samples to walk this round, by walk class (classify_kernel):
+                                  // 0 = receiving (carrier detect on, in or between frames), 1 = everything else
     uint32_t* dec_list;           // [5][Np] streams with a completed frame, by decode kind (0..3 = Viterbi map, 4 = LICH / none)
     float* sw_samples;            // [30][Np]
     float* fir_snap;              // [149][Np]
@@ -173,6 +175,7 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
 void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
+void launch_classify(const DevPtrs& d, uint32_t head, cudaStream_t s);
 void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);

@@ -166,7 +166,7 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
 #pragma unroll 1
     for (int pass = 0; pass != kFirPasses; ++pass) {
         const int o0 = pass * kFirPass + warp * kFirOut;              // first output of this thread in the tile
-        if (tb + (uint32_t) o0 >= head + n_new) break;                // nothing new from here on (warp-uniform)
+        if ((int32_t) (tb + (uint32_t) o0 - (head + n_new)) >= 0) break;   // nothing new from here on (warp-uniform; positions wrap)
         const float* row = xs + lane * kFirRow + kFirHalo + o0;        // sample t0
         Acc2 acc2[kFirOut / 2];
         float acc[kFirOut], w[kFirOut];
@@ -302,24 +302,74 @@ void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned lo
     dcd_kernel<<<(2 * d.n_streams + 127) / 128, 128, 0, s>>>(d, head_old, n_new, head64_old);
 }
 
+// Which streams have samples to walk this round, and how: the lanes of a warp run in lock-step, so a warp moves at
+// the pace of its slowest lane, and a stream that is acquiring (start-up, sync-word search, preamble: the state
+// machine acts on every symbol or every sample) is an order of magnitude slower per sample than one that is
+// receiving frames (one slicer decision per symbol).  With streams mapped to lanes by index nearly every warp
+// carries one of the few slow ones.  classify_kernel therefore sorts the streams that have work into two lists
+// and scan_kernel's warps each take 32 entries of ONE list (per-stream state is then gathered rather than
+// coalesced: a few hundred bytes per stream and round).
+__global__ void __launch_bounds__(256)
+classify_kernel(DevPtrs d, uint32_t head)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    int cls = -1;
+    bool lag = false;
+    if (s < d.n_streams) {
+        const uint32_t* sb = d.st + st_index(s, 0);
+        const uint32_t pos = sb[F_POS * 32], fl = sb[F_FLAGS * 32];
+        if (pos != head) {
+            if (fl & (FL_PENDING | FL_FIXUP)) lag = true;       // waits for decode_kernel / fixup_kernel: not at the head yet
+            else {
+                const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
+                const bool receiving = (fl & FL_DCD) && (sb[F_CNT * 32] >> 16) == 0 && (sb[F_IDX * 32] >> 24) >= (uint32_t) kTapsUsed &&
+                                       (st == ST_FRAME || st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT);
+                cls = receiving ? 0 : 1;
+            }
+        }
+    }
+    const uint32_t lane = threadIdx.x & 31u;
+#pragma unroll
+    for (int c = 0; c != 2; ++c) {
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, cls == c);
+        if (m) {
+            uint32_t base = 0;
+            if (lane == (uint32_t) (__ffs((int) m) - 1)) base = atomicAdd(&d.ctr->scan_count[c], (unsigned) __popc(m));
+            base = __shfl_sync(0xFFFFFFFFu, base, __ffs((int) m) - 1);
+            if (cls == c) d.scan_list[(size_t) c * d.np + base + (uint32_t) __popc(m & ((1u << lane) - 1u))] = s;
+        }
+    }
+    const uint32_t ml = __ballot_sync(0xFFFFFFFFu, lag);
+    if (ml && lane == 0) atomicAdd(&d.ctr->lagging, (unsigned) __popc(ml));
+}
+
+void launch_classify(const DevPtrs& d, uint32_t head, cudaStream_t s)
+{
+    classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head);
+}
+
 __global__ void __launch_bounds__(kScanThreads)
-scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard)
+scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls)
 {
     __shared__ LlrTable tab;                               // lanes look up different entries: shared, not constant memory
     const int tid = threadIdx.x;
+    const uint32_t g = blockIdx.x * kScanThreads + tid;    // thread g takes the g-th entry of the class's list
+    const uint32_t n = d.ctr->scan_count[cls];
+    if (blockIdx.x * kScanThreads >= n) return;            // CTA-uniform
     for (int i = tid; i < 48; i += kScanThreads) tab.thr[i] = llr_thr_padded(c_tab.llr_thr, i);
     for (int i = tid; i < 43; i += kScanThreads) {
         tab.val[i] = (uint32_t) (uint8_t) c_tab.llr_val[i][0] | ((uint32_t) (uint8_t) c_tab.llr_val[i][1] << 8);
     }
     __syncthreads();
-    const uint32_t s = blockIdx.x * kScanThreads + tid;
-    if (s >= d.n_streams) return;
+    if (g >= n) return;
+    const uint32_t s = d.scan_list[(size_t) cls * d.np + g];
     scan_lane(d, make_io(d, s, &tab), head, head64, true, defer != 0, guard);
 }
 
 void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s)
 {
-    scan_kernel<<<d.np / kScanThreads, kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard);
+    for (int cls = 0; cls != 2; ++cls)
+        scan_kernel<<<d.np / kScanThreads, kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard, cls);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to
@@ -404,6 +454,7 @@ search_limit_kernel(DevPtrs d, uint32_t head)
     if (!wants_search(sb, head)) return;
     const uint32_t lmask = d.ring_lines - 1;
     const uint32_t from = sb[F_POS * 32];
+    head = search_end(from, head);
     Biquad b;
     b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
     // blocks from the one that contains `from`; the next block's samples are requested a block of arithmetic ahead
@@ -434,15 +485,16 @@ search_limit_kernel(DevPtrs d, uint32_t head)
 constexpr int kMaskThreads = 128;
 
 __global__ void __launch_bounds__(kMaskThreads)
-search_mask_kernel(DevPtrs d, uint32_t head)
+search_mask_kernel(DevPtrs d, uint32_t head_all)
 {
     const uint32_t n_req = d.ctr->fix_count;
     const uint32_t lmask = d.ring_lines - 1;
     for (uint32_t q = blockIdx.y; q < n_req; q += gridDim.y) {
         const uint32_t s = d.fix_list[q];
         uint32_t* sb = d.st + st_index(s, 0);
-        const bool search = wants_search(sb, head);                 // CTA-uniform
+        const bool search = wants_search(sb, head_all);             // CTA-uniform
         const bool first = blockIdx.x == 0 && threadIdx.x == 0;
+        const uint32_t head = search_end(sb[F_POS * 32], head_all);
         if (search) {
             const uint32_t from = sb[F_POS * 32];
             const int k0 = (int) (sb[F_IDX * 32] >> 24);            // samples clocked since the last resume, before `from`
@@ -512,7 +564,7 @@ void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
     fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head);
     search_limit_kernel<<<d.np / 128, 128, 0, s>>>(d, head);
     // a request's span is at most the ring: x = its blocks in strides of the grid, y = requests in strides of the grid
-    search_mask_kernel<<<dim3(8, (unsigned) sm_count * 2), kMaskThreads, 0, s>>>(d, head);
+    search_mask_kernel<<<dim3(2, (unsigned) sm_count * 4), kMaskThreads, 0, s>>>(d, head);
 }
 
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)

@@ -1411,6 +1411,8 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                 if (!z.dcd) { gate_off(d, e, z.gap_k, pos); break; }
             }
             if (pos == head || z.pending || z.state == ST_UNLOCKED) break;
+            // inside a frame with nothing pending at index() == 0: the rest of the frame is the frame walk's
+            if (!initializing && z.state == ST_FRAME && !z.need_reset && !z.need_update && z.gap_k >= kTapsUsed) break;
         }
     }
 
@@ -1526,6 +1528,15 @@ M17B_FN bool wants_search(const uint32_t* sb, uint32_t head)
            sb[F_POS * 32] != head;
 }
 
+// End of the span a search request covers: the stream usually finds its sync word within a frame's worth of
+// samples, and what lies beyond would be searched for nothing (and keeps the whole round waiting: the limit
+// filter over the span is a serial recurrence).  A stream that is still searching at the end asks again.
+constexpr uint32_t kSearchSpan = 2048;
+M17B_FN uint32_t search_end(uint32_t from, uint32_t head)
+{
+    return head - from > kSearchSpan ? from + kSearchSpan : head;
+}
+
 // One sample of the search pass: the limit filter step and the trigger decisions of the preamble, LSF /
 // stream and packet / BERT sync words (the words do_unlocked looks for, M17Demodulator.h:288-342) for the
 // sample at p, the k-th clocked one since the last resume.  Returns bit w = word w triggers.
@@ -1546,6 +1557,7 @@ M17B_FN void search_lane(const DevPtrs& d, uint32_t s, uint32_t head)
     if (!wants_search(sb, head)) return;
     const LaneIo e = make_io(d, s, nullptr);
     const uint32_t from = sb[F_POS * 32];
+    head = search_end(from, head);
     Biquad b;
     b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
     int k = (int) (sb[F_IDX * 32] >> 24);
