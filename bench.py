@@ -312,7 +312,7 @@ def main():
     fir_ms_per_launch = prof_alone.fir_ms / max(1, prof_alone.fir_launches)
     fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
-    kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "decode": prof.decode_ms, "fixup_search": prof.fixup_ms,
+    kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "scan_acquiring": prof.scan1_ms, "decode": prof.decode_ms, "fixup_search": prof.fixup_ms,
                  "tail": prof.aux_ms}
     ksum = sum(kernel_ms.values()) or 1.0
     launches = int(prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches +

@@ -57,10 +57,12 @@ extern "C" {
 #define M17B_INVERT      0x2u  /* `sample *= -1` before scaling (apps/m17-demod.cpp:488, -i)   */
 #define M17B_PROFILE     0x4u  /* record CUDA events around every kernel (m17b_get_profile)    */
 #define M17B_STREAMING   0x8u  /* back-to-back submits (m17b_ticket / m17b_drain_upto): between submits a
-                                * stream may trail the newest sample by less than one frame, so that it
-                                * always walks whole frames.  Every frame that ends inside a submit is still
-                                * delivered with that submit; m17b_sync / m17b_drain bring all streams up to
-                                * the newest sample first (their diagnostics then match the reference's).  */
+                                * stream may trail the newest sample, so that it always walks whole frames.
+                                * A stream that is receiving delivers every frame that ends inside a submit
+                                * with that submit; one that is acquiring (idle, searching for sync words, in
+                                * a preamble) is served at a lower rate and may deliver up to two submits
+                                * later.  m17b_sync / m17b_drain bring all streams up to the newest sample
+                                * first (their diagnostics then match the reference's).  */
 
 #define M17B_DIAG_RECORDS 0x10u /* record one m17b_diag_rec per reference diagnostic callback (m17b_diag_drain);
                                  * for few-channel callers such as the CLI: 56 bytes per 384 / 960 samples and stream */
@@ -154,6 +156,7 @@ typedef struct m17b_profile {
     double   dcd_ms;     uint64_t dcd_launches;                              /* carrier-detect pre-pass          */
     double   fixup_ms;   uint64_t fixup_launches;                            /* filter fix-up + sync-word search */
     uint64_t search_requests; uint64_t search_samples;                       /* searches served / samples covered */
+    double   scan1_ms;                                                       /* scan of the acquiring streams (walk class 1; scan_ms = receiving streams) */
 } m17b_profile;
 
 uint32_t    m17b_version(void);

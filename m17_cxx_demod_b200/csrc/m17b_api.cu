@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -41,6 +42,9 @@ struct m17b_ctx {
     // while the rounds of submit k run on `compute`; ev_front = front end of the newest submit done,
     // ev_rounds[k & 1] = rounds of submit k done (the front end may be one submit ahead, not two)
     cudaStream_t front = nullptr;
+    cudaStream_t aux = nullptr;                // chain of walk class 1 of a round (run_round)
+    cudaEvent_t ev_cls = nullptr, ev_aux = nullptr;
+    bool aux_running = false;                  // an aux chain has been enqueued that `compute` has not waited for yet
     cudaEvent_t ev_front = nullptr, ev_rounds[2] = {nullptr, nullptr};
     unsigned long long n_submits = 0;
     uint32_t head = 0;
@@ -69,7 +73,7 @@ struct m17b_ctx {
 
 namespace {
 
-enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H, CAT_DCD, CAT_FIXUP };
+enum { CAT_FIR, CAT_SCAN, CAT_DECODE, CAT_AUX, CAT_H2D, CAT_D2H, CAT_DCD, CAT_FIXUP, CAT_SCAN1 };
 
 int fail(m17b_ctx* c, cudaError_t e, const char* what)
 {
@@ -110,6 +114,7 @@ void ev_collect(m17b_ctx* c)
             case CAT_H2D: c->prof.h2d_ms += ms; break;
             case CAT_DCD: c->prof.dcd_ms += ms; break;
             case CAT_FIXUP: c->prof.fixup_ms += ms; break;
+            case CAT_SCAN1: c->prof.scan1_ms += ms; break;
             default: c->prof.d2h_ms += ms; break;
             }
         }
@@ -118,23 +123,44 @@ void ev_collect(m17b_ctx* c)
     c->ev_live.clear();
 }
 
-int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard = 0)
+// One round: every stream that has samples to walk advances to its next completed frame (or until it needs
+// fixup_kernel), the completed frames are decoded, the fix-up / search requests served.  The streams are sorted
+// into two walk classes first (classify_kernel) and each class runs its own chain scan -> decode -> fix-up: the
+// receiving streams (class 0) on `st`, the acquiring ones (class 1: idle, start-up, sync-word search, preamble)
+// on the aux stream beside it.  The acquiring streams are few, but theirs are long serial walks -- a round of them
+// takes as long as two or three rounds of the receiving streams -- so with `with_aux` clear a round lists the
+// receiving streams only and leaves the aux chain of an earlier round running; the flags word of a stream is
+// what hands it from one chain to the other (see scan_lane's write-back).  `wait_end`: the round ends when both
+// chains have.
+int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard, bool with_aux, bool wait_end)
 {
     EvPair p{};
-    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 10 * sizeof(unsigned int), st));     // lagging, fix_count, dec_count[5], deferred, scan_count[2]
-    ev_begin(c, st, CAT_SCAN, p);
-    launch_classify(c->d, c->head, st);
-    launch_scan(c->d, c->head, c->head64, defer, guard, st);
-    ev_end(c, st, p);
-    c->prof.scan_launches += 3;
-    ev_begin(c, st, CAT_DECODE, p);
-    launch_decode(c->d, c->head, c->head64, st);
-    ev_end(c, st, p);
-    c->prof.decode_launches += 1;
-    ev_begin(c, st, CAT_FIXUP, p);
-    launch_fixup(c->d, c->head, c->sm_count, st);
-    ev_end(c, st, p);
-    c->prof.fixup_launches += 3;
+    if (with_aux && c->aux_running) { CK(cudaStreamWaitEvent(st, c->ev_aux, 0)); c->aux_running = false; }
+    // lagging, deferred and the work lists of the classes this round runs
+    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 2 * sizeof(unsigned int) + (with_aux ? 2 : 1) * sizeof(ClassCounters), st));
+    launch_classify(c->d, c->head, with_aux ? 3u : 1u, st);
+    if (with_aux) {
+        CK(cudaEventRecord(c->ev_cls, st));
+        CK(cudaStreamWaitEvent(c->aux, c->ev_cls, 0));
+    }
+    for (int cls = with_aux ? 1 : 0; cls >= 0; --cls) {
+        cudaStream_t s = cls ? c->aux : st;
+        ev_begin(c, s, cls ? CAT_SCAN1 : CAT_SCAN, p);
+        launch_scan(c->d, c->head, c->head64, defer, guard, cls, s);
+        ev_end(c, s, p);
+        ev_begin(c, s, CAT_DECODE, p);
+        launch_decode(c->d, c->head, c->head64, cls, s);
+        ev_end(c, s, p);
+        ev_begin(c, s, CAT_FIXUP, p);
+        launch_fixup(c->d, c->head, c->sm_count, cls, s);
+        ev_end(c, s, p);
+        if (cls) { CK(cudaEventRecord(c->ev_aux, s)); c->aux_running = true; }
+        c->prof.scan_launches += 1;
+        c->prof.decode_launches += 1;
+        c->prof.fixup_launches += 3;
+    }
+    c->prof.scan_launches += 1;      // classify_kernel
+    if (wait_end && c->aux_running) { CK(cudaStreamWaitEvent(st, c->ev_aux, 0)); c->aux_running = false; }
     CK(cudaGetLastError());
     return M17B_OK;
 }
@@ -189,6 +215,7 @@ void free_all(m17b_ctx* c)
     if (c->copy) cudaStreamSynchronize(c->copy);
     if (c->d2h) cudaStreamSynchronize(c->d2h);
     if (c->front) cudaStreamSynchronize(c->front);
+    if (c->aux) cudaStreamSynchronize(c->aux);
     for (auto& p : c->ev_live) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& p : c->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
@@ -208,6 +235,9 @@ void free_all(m17b_ctx* c)
     if (c->copy) cudaStreamDestroy(c->copy);
     if (c->d2h) cudaStreamDestroy(c->d2h);
     if (c->front) cudaStreamDestroy(c->front);
+    if (c->aux) cudaStreamDestroy(c->aux);
+    if (c->ev_cls) cudaEventDestroy(c->ev_cls);
+    if (c->ev_aux) cudaEventDestroy(c->ev_aux);
     if (c->ev_front) cudaEventDestroy(c->ev_front);
     for (auto& e : c->ev_rounds) if (e) cudaEventDestroy(e);
     delete c;
@@ -265,6 +295,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
             CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
             CK(cudaStreamCreateWithPriority(&c->compute, cudaStreamNonBlocking, prio_hi));
             CK(cudaStreamCreateWithPriority(&c->front, cudaStreamNonBlocking, prio_lo));
+            CK(cudaStreamCreateWithPriority(&c->aux, cudaStreamNonBlocking, prio_hi));
+            CK(cudaEventCreateWithFlags(&c->ev_cls, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&c->ev_front, cudaEventDisableTiming));
             for (auto& e : c->ev_rounds) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
@@ -309,9 +342,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
         CK(cudaMalloc(&d.seg_ring, (size_t) d.n_seg * 4 * np * sizeof(float)));
         CK(cudaMemsetAsync(d.seg_ring, 0, (size_t) d.n_seg * 4 * np * sizeof(float), c->compute));
-        CK(cudaMalloc(&d.fix_list, np * sizeof(uint32_t)));
-        CK(cudaMalloc(&d.scan_list, 2 * np * sizeof(uint32_t)));
-        CK(cudaMalloc(&d.dec_list, 5 * np * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.fix_list, kClasses * np * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.scan_list, kClasses * np * sizeof(uint32_t)));
+        CK(cudaMalloc(&d.dec_list, kClasses * 5 * np * sizeof(uint32_t)));
         CK(cudaMalloc(&d.sw_samples, 30 * np * sizeof(float)));
         CK(cudaMalloc(&d.fir_snap, (size_t) kTapsUsed * np * sizeof(float)));
         CK(cudaMalloc(&d.llr, 184 * np * sizeof(int16_t)));
@@ -463,7 +496,10 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     // worth of serial latency however few lanes run; the next submit's front end fills the machine meanwhile.
     const int rounds = (int) (n / kMinFrameSpacing) + 2;
     for (int r = 0; r != rounds; ++r) {
-        int rc = run_round(c, streaming, c->compute, streaming ? c->cfg.max_chunk : 0u);
+        // M17B_STREAMING: the acquiring streams get every third round (their rounds are long, and they may trail the
+        // head by more than a submit: the ring is doubled); otherwise every round, so that all streams reach the head
+        const bool with_aux = !streaming || r % 3 == 0;
+        int rc = run_round(c, streaming, c->compute, streaming ? c->cfg.max_chunk : 0u, with_aux, !streaming || r == rounds - 1);
         if (rc != M17B_OK) return rc;
     }
     if (streaming) CK(cudaEventRecord(c->ev_rounds[c->n_submits & 1], c->compute));
@@ -485,7 +521,7 @@ int m17b_sync(m17b_ctx* c)
     if (rc != M17B_OK) return rc;
     for (int extra = 0; c->host_ctr.lagging != 0 || c->host_ctr.deferred != 0; ++extra) {
         if (extra == 256) { c->last_error = "streams failed to reach the head"; return M17B_ESTATE; }
-        if ((rc = run_round(c, false, c->compute)) != M17B_OK) return rc;
+        if ((rc = run_round(c, false, c->compute, 0, true, true)) != M17B_OK) return rc;
         if ((rc = fetch_counters(c)) != M17B_OK) return rc;
     }
     ev_collect(c);

@@ -49,6 +49,7 @@ constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:14
 constexpr int kRoundCap = 2048;       // ring slack: samples a stream may trail the head by beyond one submit
 constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
 constexpr int kSeg = 192;             // gcd of the carrier-detect cadences 384 / 960 and of the 1920-sample start-up
+constexpr int kClasses = 2;           // walk classes a round sorts the streams into (classify_kernel)
 constexpr int kFirstUpdate = 1920 + 384;   // position of a stream's first carrier-detect update (M17Demodulator.h:659-689)
 
 enum Field : int {
@@ -94,6 +95,13 @@ enum DemodState : int { ST_UNLOCKED, ST_LSF_SYNC, ST_STREAM_SYNC, ST_PACKET_SYNC
 enum DecState : int { DEC_LSF, DEC_STREAM, DEC_BASIC_PACKET, DEC_FULL_PACKET, DEC_BERT };
 enum SyncType : int { SW_LSF, SW_STREAM, SW_PACKET, SW_BERT };
 
+struct ClassCounters {            // work lists of one walk class, reset before the class's chain of a round runs
+    unsigned int scan_count;      // entries in scan_list
+    unsigned int fix_count;       // entries in fix_list
+    unsigned int dec_count[5];    // entries in dec_list per decode kind
+    unsigned int pad;
+};
+
 struct Counters {                 // device-side mirror of m17b_counters (+ record ring cursor)
     unsigned long long frames[6];
     unsigned long long lsf_crc_fail;
@@ -101,12 +109,10 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned long long faults;
     unsigned long long dropped;
     unsigned int rec_count;       // record cursor: records appended so far (monotonic, mod 2^32)
-    unsigned int lagging;         // streams that have not reached head (set by the scan kernel)
-    unsigned int fix_count;       // entries in fix_list (reset with lagging before every scan)
-    unsigned int dec_count[5];    // entries in dec_list per decode kind (reset likewise)
-    unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
-    unsigned int scan_count[2];   // entries in scan_list per walk class (reset likewise)
     unsigned int diag_count;      // diagnostic-record cursor (M17B_DIAG_RECORDS), monotonic like rec_count
+    unsigned int lagging;         // streams that have not reached head (reset before every round)
+    unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
+    ClassCounters cls[kClasses];
     unsigned long long diag_dropped;
     unsigned long long search_requests;   // sync-word searches served by search_mask_kernel
     unsigned long long search_samples;    // ... and the samples they covered
@@ -121,10 +127,11 @@ struct DevPtrs {
     float* corr_snap;             // [80][Np] the correlator's last 80 samples before a carrier-detect gap
     float* seg_ring;              // [n_seg][4][Np] carrier-detect energy sums per window start (see dcd_lane)
     float2* ckpt_ring;            // [RL][Np][4] limit-filter history after every 8-sample block of a searched span
-    uint32_t* fix_list;           // [Np] streams waiting for fixup_kernel
-    uint32_t* scan_list;          // [2][Np] streams with samples to walk this round, by walk class (classify_kernel):
-                                  // 0 = receiving (carrier detect on, in or between frames), 1 = everything else
-    uint32_t* dec_list;           // [5][Np] streams with a completed frame, by decode kind (0..3 = Viterbi map, 4 = LICH / none)
+    uint32_t* fix_list;           // [kClasses][Np] streams waiting for fixup_kernel, by the walk class that asked
+    uint32_t* scan_list;          // [kClasses][Np] streams with samples to walk this round, by walk class (classify_kernel):
+                                  // 0 = receiving (carrier detect on, in or between frames), 1 = everything else (idle,
+                                  // start-up, sync-word search, preamble, after a carrier-detect gap)
+    uint32_t* dec_list;           // [kClasses][5][Np] streams with a completed frame, by walk class and decode kind (0..3 = Viterbi map, 4 = LICH / none)
     float* sw_samples;            // [30][Np]
     float* fir_snap;              // [149][Np]
     int16_t* llr;                 // [184][Np]
@@ -175,10 +182,10 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
 void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
-void launch_classify(const DevPtrs& d, uint32_t head, cudaStream_t s);
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s);
-void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s);
-void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s);
+void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, cudaStream_t s);
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, cudaStream_t s);
+void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, int cls, cudaStream_t s);
+void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, int cls, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);
 void launch_init_state(const DevPtrs& d, uint32_t origin, cudaStream_t s);
 void launch_debug_corr(const DevPtrs& d, uint32_t n, float* out, cudaStream_t s);

@@ -230,6 +230,8 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
     uint32_t span = head + n_new - b0;
     dim3 grid(d.np / kFirStreams, (span + kFirTile - 1) / kFirTile);
     size_t smem = sizeof(float) * kFirStreams * kFirRow;
+    static const int pad_kb = getenv("M17B_FIR_PAD_KB") ? atoi(getenv("M17B_FIR_PAD_KB")) : 0;     // experiment: fewer CTAs per SM
+    smem += (size_t) pad_kb * 1024;
     // 16-byte loads need the chunk to start on a ring-chunk boundary and 16-byte aligned rows
     int aligned = (head % 8 == 0) && (stride % 8 == 0) && (reinterpret_cast<uintptr_t>(in) % 16 == 0) &&
                   (reinterpret_cast<uintptr_t>(tail) % 16 == 0);
@@ -306,18 +308,22 @@ void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned lo
 // the pace of its slowest lane, and a stream that is acquiring (start-up, sync-word search, preamble: the state
 // machine acts on every symbol or every sample) is an order of magnitude slower per sample than one that is
 // receiving frames (one slicer decision per symbol).  With streams mapped to lanes by index nearly every warp
-// carries one of the few slow ones.  classify_kernel therefore sorts the streams that have work into two lists
+// carries one of the few slow ones.  classify_kernel therefore sorts the streams that have work into kClasses lists
 // and scan_kernel's warps each take 32 entries of ONE list (per-stream state is then gathered rather than
 // coalesced: a few hundred bytes per stream and round).
 __global__ void __launch_bounds__(256)
-classify_kernel(DevPtrs d, uint32_t head)
+classify_kernel(DevPtrs d, uint32_t head, uint32_t class_mask /* bit c: list class c this round */)
 {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     int cls = -1;
     bool lag = false;
     if (s < d.n_streams) {
-        const uint32_t* sb = d.st + st_index(s, 0);
-        const uint32_t pos = sb[F_POS * 32], fl = sb[F_FLAGS * 32];
+        const volatile uint32_t* sb = d.st + st_index(s, 0);
+        // the flags word first: a stream whose flags make it this round's is complete (scan_lane / decode_lane
+        // publish the flags last); one that another chain still works on shows flags that are not
+        const uint32_t fl = sb[F_FLAGS * 32];
+        __threadfence();
+        const uint32_t pos = sb[F_POS * 32];
         if (pos != head) {
             if (fl & (FL_PENDING | FL_FIXUP)) lag = true;       // waits for decode_kernel / fixup_kernel: not at the head yet
             else {
@@ -325,16 +331,17 @@ classify_kernel(DevPtrs d, uint32_t head)
                 const bool receiving = (fl & FL_DCD) && (sb[F_CNT * 32] >> 16) == 0 && (sb[F_IDX * 32] >> 24) >= (uint32_t) kTapsUsed &&
                                        (st == ST_FRAME || st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT);
                 cls = receiving ? 0 : 1;
+                if (!((class_mask >> cls) & 1u)) { cls = -1; lag = true; }     // its class sits this round out
             }
         }
     }
     const uint32_t lane = threadIdx.x & 31u;
 #pragma unroll
-    for (int c = 0; c != 2; ++c) {
+    for (int c = 0; c != kClasses; ++c) {
         const uint32_t m = __ballot_sync(0xFFFFFFFFu, cls == c);
         if (m) {
             uint32_t base = 0;
-            if (lane == (uint32_t) (__ffs((int) m) - 1)) base = atomicAdd(&d.ctr->scan_count[c], (unsigned) __popc(m));
+            if (lane == (uint32_t) (__ffs((int) m) - 1)) base = atomicAdd(&d.ctr->cls[c].scan_count, (unsigned) __popc(m));
             base = __shfl_sync(0xFFFFFFFFu, base, __ffs((int) m) - 1);
             if (cls == c) d.scan_list[(size_t) c * d.np + base + (uint32_t) __popc(m & ((1u << lane) - 1u))] = s;
         }
@@ -343,48 +350,55 @@ classify_kernel(DevPtrs d, uint32_t head)
     if (ml && lane == 0) atomicAdd(&d.ctr->lagging, (unsigned) __popc(ml));
 }
 
-void launch_classify(const DevPtrs& d, uint32_t head, cudaStream_t s)
+void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, cudaStream_t s)
 {
-    classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head);
+    classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head, class_mask);
 }
+
+// The acquiring streams (class 1) are few and each is in a different part of the state machine: 32 of them in
+// a warp run one after the other (3 of 32 lanes active per instruction, measured), and the round waits for the
+// slowest warp.  They are spread over kSpread times as many warps instead, every kSpread-th lane active, which
+// divides a warp's serial chain by as much.
+constexpr int kSpread = 1;
 
 __global__ void __launch_bounds__(kScanThreads)
 scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls)
 {
     __shared__ LlrTable tab;                               // lanes look up different entries: shared, not constant memory
     const int tid = threadIdx.x;
-    const uint32_t g = blockIdx.x * kScanThreads + tid;    // thread g takes the g-th entry of the class's list
-    const uint32_t n = d.ctr->scan_count[cls];
-    if (blockIdx.x * kScanThreads >= n) return;            // CTA-uniform
+    const uint32_t t = blockIdx.x * kScanThreads + tid;
+    const uint32_t spread = cls ? (uint32_t) kSpread : 1u;
+    const uint32_t g = t / spread;                         // thread takes the g-th entry of the class's list
+    const uint32_t n = d.ctr->cls[cls].scan_count;
+    if (blockIdx.x * kScanThreads / spread >= n) return;   // CTA-uniform
     for (int i = tid; i < 48; i += kScanThreads) tab.thr[i] = llr_thr_padded(c_tab.llr_thr, i);
     for (int i = tid; i < 43; i += kScanThreads) {
         tab.val[i] = (uint32_t) (uint8_t) c_tab.llr_val[i][0] | ((uint32_t) (uint8_t) c_tab.llr_val[i][1] << 8);
     }
     __syncthreads();
-    if (g >= n) return;
+    if (g >= n || t % spread != 0) return;
     const uint32_t s = d.scan_list[(size_t) cls * d.np + g];
-    scan_lane(d, make_io(d, s, &tab), head, head64, true, defer != 0, guard);
+    scan_lane(d, make_io(d, s, &tab, cls), head, head64, true, defer != 0, guard);
 }
 
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, cudaStream_t s)
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, cudaStream_t s)
 {
-    for (int cls = 0; cls != 2; ++cls)
-        scan_kernel<<<d.np / kScanThreads, kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard, cls);
+    scan_kernel<<<d.np / kScanThreads * (cls ? kSpread : 1), kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard, cls);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to
 // whole warps: all lanes of a warp decode the same kind of frame (same Viterbi length and map).
 __global__ void __launch_bounds__(kDecThreads)
-decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
+decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int cls)
 {
     extern __shared__ uint16_t hist[];                     // [244][128] survivor decisions
     uint32_t g = blockIdx.x * kDecThreads + threadIdx.x;
     uint32_t s = 0xFFFFFFFFu;
 #pragma unroll
     for (int k = 0; k != 5; ++k) {
-        const uint32_t n = d.ctr->dec_count[k], padded = (n + 31u) & ~31u;
+        const uint32_t n = d.ctr->cls[cls].dec_count[k], padded = (n + 31u) & ~31u;
         if (s == 0xFFFFFFFFu) {
-            if (g < padded) { s = g < n ? d.dec_list[(size_t) k * d.np + g] : 0xFFFFFFFEu; }
+            if (g < padded) { s = g < n ? d.dec_list[(size_t) (cls * 5 + k) * d.np + g] : 0xFFFFFFFEu; }
             else g -= padded;
         }
     }
@@ -412,14 +426,15 @@ decode_kernel(DevPtrs d, uint32_t head, unsigned long long head64)
 constexpr int kFixThreads = 160;
 
 __global__ void __launch_bounds__(kFixThreads)
-fixup_kernel(DevPtrs d, uint32_t head)
+fixup_kernel(DevPtrs d, uint32_t head, int cls)
 {
     __shared__ float xs[kTapsUsed], snap[kTapsUsed];
-    const uint32_t n_req = d.ctr->fix_count;
+    const uint32_t n_req = d.ctr->cls[cls].fix_count;
+    const uint32_t* const fix_list = d.fix_list + (size_t) cls * d.np;
     const uint32_t cmask = d.ring_lines - 1;
     const int t = threadIdx.x;
     for (uint32_t q = blockIdx.x; q < n_req; q += gridDim.x) {
-        const uint32_t s = d.fix_list[q];
+        const uint32_t s = fix_list[q];
         uint32_t* sb = d.st + st_index(s, 0);
         const uint32_t R = sb[F_GAPR * 32];
         const int done = (int) sb[F_GAPDONE * 32];
@@ -445,11 +460,11 @@ fixup_kernel(DevPtrs d, uint32_t head)
 }
 
 __global__ void __launch_bounds__(128)
-search_limit_kernel(DevPtrs d, uint32_t head)
+search_limit_kernel(DevPtrs d, uint32_t head, int cls)
 {
     const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= d.ctr->fix_count) return;
-    const uint32_t s = d.fix_list[q];
+    if (q >= d.ctr->cls[cls].fix_count) return;
+    const uint32_t s = d.fix_list[(size_t) cls * d.np + q];
     const uint32_t* sb = d.st + st_index(s, 0);
     if (!wants_search(sb, head)) return;
     const uint32_t lmask = d.ring_lines - 1;
@@ -485,12 +500,13 @@ search_limit_kernel(DevPtrs d, uint32_t head)
 constexpr int kMaskThreads = 128;
 
 __global__ void __launch_bounds__(kMaskThreads)
-search_mask_kernel(DevPtrs d, uint32_t head_all)
+search_mask_kernel(DevPtrs d, uint32_t head_all, int cls)
 {
-    const uint32_t n_req = d.ctr->fix_count;
+    const uint32_t n_req = d.ctr->cls[cls].fix_count;
+    const uint32_t* const fix_list = d.fix_list + (size_t) cls * d.np;
     const uint32_t lmask = d.ring_lines - 1;
     for (uint32_t q = blockIdx.y; q < n_req; q += gridDim.y) {
-        const uint32_t s = d.fix_list[q];
+        const uint32_t s = fix_list[q];
         uint32_t* sb = d.st + st_index(s, 0);
         const bool search = wants_search(sb, head_all);             // CTA-uniform
         const bool first = blockIdx.x == 0 && threadIdx.x == 0;
@@ -559,18 +575,18 @@ search_mask_kernel(DevPtrs d, uint32_t head_all)
     }
 }
 
-void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, cudaStream_t s)
+void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, int cls, cudaStream_t s)
 {
-    fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head);
-    search_limit_kernel<<<d.np / 128, 128, 0, s>>>(d, head);
-    // a request's span is at most the ring: x = its blocks in strides of the grid, y = requests in strides of the grid
-    search_mask_kernel<<<dim3(2, (unsigned) sm_count * 4), kMaskThreads, 0, s>>>(d, head);
+    fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head, cls);
+    search_limit_kernel<<<d.np / 128, 128, 0, s>>>(d, head, cls);
+    // a request's span is at most kSearchSpan + 7 samples: x = its blocks, y = requests in strides of the grid
+    search_mask_kernel<<<dim3(2, (unsigned) sm_count * 4), kMaskThreads, 0, s>>>(d, head, cls);
 }
 
-void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, cudaStream_t s)
+void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, int cls, cudaStream_t s)
 {
     size_t smem = sizeof(uint16_t) * 244 * kDecThreads;
-    decode_kernel<<<(d.np + 5 * 32 + kDecThreads - 1) / kDecThreads, kDecThreads, smem, s>>>(d, head, head64);
+    decode_kernel<<<(d.np + 5 * 32 + kDecThreads - 1) / kDecThreads, kDecThreads, smem, s>>>(d, head, head64, cls);
 }
 
 // Per-device kernel attributes (dynamic shared memory above 48 KiB).
@@ -580,10 +596,10 @@ cudaError_t configure_kernels()
                              (int) (sizeof(uint16_t) * 244 * kDecThreads));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(fir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int) (sizeof(float) * kFirStreams * kFirRow));
+                             (int) (sizeof(float) * kFirStreams * kFirRow) + 64 * 1024);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(fir_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int) (sizeof(float) * kFirStreams * kFirRow));
+                                (int) (sizeof(float) * kFirStreams * kFirRow) + 64 * 1024);
 }
 
 __global__ void init_state_kernel(DevPtrs d, uint32_t origin)

@@ -74,8 +74,12 @@ M17B_FN unsigned int ctr_add(unsigned int* p, unsigned int v) { unsigned int o =
 
 #ifdef __CUDACC__
 M17B_FN int first_set(uint32_t m) { return __ffs((int) m) - 1; }
+M17B_FN void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+M17B_FN void publish_fence() { __threadfence(); }
 #else
 M17B_FN int first_set(uint32_t m) { return __builtin_ffs((int) m) - 1; }
+M17B_FN void prefetch_l2(const void*) {}
+M17B_FN void publish_fence() {}
 #endif
 
 // ---------------------------------------------------------------------------
@@ -196,6 +200,7 @@ struct LaneIo {
     const uint32_t* mask_ring;
     const float2* ckpt_ring;
     uint32_t np, lmask, s;
+    int cls;               // walk class the lane was listed in (selects the work lists it appends to)
 };
 
 M17B_FN size_t ring_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
@@ -322,7 +327,8 @@ M17B_FN_COLD uint32_t sync_step(float* samples, size_t np, float value, int idx1
 // samples clocked since the last resume.  Returns (offset, idev); dev.reset_ is always false afterwards.
 struct F2 { float x, y; };
 
-M17B_FN_COLD F2 update_values(uint32_t* sb, const LaneIo& e, int si, int pp, uint32_t p, int k, bool dev_reset)
+// y8 (may be null): the samples 70, 60, ..., 0 steps back, when the caller holds them and pp = si (mod 10).
+M17B_FN_COLD F2 update_values(uint32_t* sb, const LaneIo& e, int si, int pp, uint32_t p, int k, bool dev_reset, const float* y8)
 {
     float min_sum = 0, max_sum = 0;
     int min_count = 0, max_count = 0;
@@ -331,7 +337,7 @@ M17B_FN_COLD F2 update_values(uint32_t* sb, const LaneIo& e, int si, int pp, uin
     for (int i = si; i < 80; i += 10) {
         int d = pp - i;
         d = d < 0 ? d + 80 : d;
-        lv[n++] = y_back(e, p, k, d);
+        lv[n++] = y8 ? y8[7 - d / 10] : y_back(e, p, k, d);
     }
     float min_level = lv[0], max_level = lv[0];
     for (int i = 0; i != n; ++i) {
@@ -491,6 +497,8 @@ struct Scan {
     // where the sample being handled gets its sync-word trigger decisions from
     float limit;                               // block walk: limit_ after it, recomputed from the block's samples when first asked for
     bool have_limit;
+    float y8[8];                               // block walk: the samples its correlations are made of (70, 60, ..., 0 steps back), loaded when first asked for
+    bool have_y8;
     uint32_t mbits;                            // search walk: the search pass's trigger bits of this sample (bit w = sync word w)
 };
 
@@ -501,7 +509,20 @@ M17B_FN float sync_value(Scan& z, const LaneIo& e, const Blk& b, uint32_t word, 
         z.limit = limit_at(b, (int) (z.p - b.base));
         z.have_limit = true;
     }
-    return sync_triggered(e, z.p, z.k, z.limit, word, m1, m2);
+    if (!z.have_y8) {                                  // every sync word of this sample correlates with the same eight
+        if (z.k > 70) {
+#pragma unroll
+            for (int i = 0; i != 8; ++i) z.y8[i] = e.ring_y[ring_off(z.p - (uint32_t) (70 - 10 * i), e.lmask, e.np, e.s)];
+        } else {
+#pragma unroll
+            for (int i = 0; i != 8; ++i) z.y8[i] = y_back(e, z.p, z.k, 70 - 10 * i);
+        }
+        z.have_y8 = true;
+    }
+    // Correlator.h:150-157
+    const float limit_1 = z.limit * m1, limit_2 = z.limit * m2;
+    const float value = corr8(z.y8, word);
+    return (value > limit_1 || value < limit_2) ? value : 0.0f;
 }
 
 // ... search walk (w: 0 preamble, 1 LSF / stream, 2 packet / BERT): the decision is the search pass's, the
@@ -513,7 +534,11 @@ M17B_FN float sync_value_masked(const Scan& z, const LaneIo& e, int w, uint32_t 
 
 #define M17B_UPDATE_VALUES(index_)                                                  \
     do {                                                                            \
-        F2 od_ = update_values(e.sb, e, z.si, z.pp, z.p, z.k, z.dev_reset);         \
+        /* (a copy: a pointer into z would put the whole working set into local memory) */ \
+        float y8c_[8];                                                              \
+        const bool use8_ = z.have_y8 && (z.pp - z.si + 80) % 10 == 0;               \
+        if (use8_) { _Pragma("unroll") for (int i_ = 0; i_ != 8; ++i_) y8c_[i_] = z.y8[i_]; } \
+        F2 od_ = update_values(e.sb, e, z.si, z.pp, z.p, z.k, z.dev_reset, use8_ ? y8c_ : nullptr); \
         z.offset = od_.x; z.idev = od_.y; z.dev_reset = false;                      \
         z.ssi = (index_);                                                           \
     } while (0)
@@ -703,31 +728,36 @@ M17B_FN void do_packet_or_bert_sync(Scan& z, const LaneIo& e, const Blk& b, bool
     }
 }
 
-// M17Demodulator.h:595-654 up to the decoder call (which decode_kernel performs)
-M17B_FN void do_frame(Scan& z, const LaneIo& e, const Blk& b, int idx /* index() of this sample = pp % 10 */)
+// ClockRecovery.h:76-88: the sample index dead-reckoned from the clock estimate, `count` samples after the
+// last update (clock_recovery.update() without an index, called half a symbol away from the symbol instant)
+M17B_FN int clock_dead_reckon(float sest, float est, uint32_t count)
 {
-    int diff = z.si - idx;
-    if (diff == 5 || diff == -5) {
-        // ClockRecovery.h:76-88
-        // fmod(v, 10) is v itself for |v| < 10 and v -+ 10 (exact) for |v| < 20; libm otherwise
-        const float v = z.ck_sest + z.ck_est * (float) z.ck_count;
-        const float av = fabsf(v);
-        float csw;
-        if (av < 10.f) csw = v;
-        else if (av < 20.f) csw = v - (v < 0 ? -10.0f : 10.0f);
-        else csw = (float) fmod((double) v, 10.0);      // exact: |result| < 10 has no more bits than v
-        // `if (csw < 0.) csw += 10; else if (csw >= 10) csw -= 10;` in double, then round:
-        // csw + 10 can need more than 24 bits, so keep that one step in double
-        int r;
-        if (csw < 0.f) r = (int) (int8_t) round((double) csw + 10.0);
-        else r = round_half_away(csw);
-        z.csi = wrap_index(r);
-        z.si = z.csi;
-        return;
+    // fmod(v, 10) is v itself for |v| < 10 and v -+ 10 (exact) for |v| < 20; libm otherwise
+    const float v = sest + est * (float) count;
+    const float av = fabsf(v);
+    float csw;
+    if (av < 10.f) csw = v;
+    else if (av < 20.f) csw = v - (v < 0 ? -10.0f : 10.0f);
+    else if (av < 16777216.f) {
+        // fmod exactly, without libm's loop: v is a multiple of its ulp (>= 2^-19 here), so v / 10 is either an
+        // integer or further from one than the division's rounding error, and v - 10 trunc(v / 10) is exact in double
+        const double dv = (double) v;
+        csw = (float) (dv - 10.0 * trunc(dv / 10.0));
     }
-    if (idx != z.si) return;
+    else csw = (float) fmod((double) v, 10.0);      // exact: |result| < 10 has no more bits than v
+    // `if (csw < 0.) csw += 10; else if (csw >= 10) csw -= 10;` in double, then round:
+    // csw + 10 can need more than 24 bits, so keep that one step in double
+    int r;
+    if (csw < 0.f) r = (int) (int8_t) round((double) csw + 10.0);
+    else r = round_half_away(csw);
+    return wrap_index(r);
+}
 
-    float sample = y_sel(b.y, (int) (z.p - b.base)) - z.offset;
+// One symbol of a frame (M17Demodulator.h:606-654 up to the decoder call): normalise, SymbolEvm, 4-FSK soft
+// decision, framer.  Sets z.pending when the symbol completes the frame.
+M17B_FN void frame_symbol(Scan& z, const LaneIo& e, float y)
+{
+    float sample = y - z.offset;
     sample *= z.idev;                                   // polarity is +1 and never changes
     // SymbolEvm.h:31-51 + StandardDeviation.h:68-72
     float err;
@@ -747,6 +777,19 @@ M17B_FN void do_frame(Scan& z, const LaneIo& e, const Blk& b, int idx /* index()
     z.sync_count = 0;
     z.pending = true;                                   // decoder(...) runs in decode_kernel
     z.state = ST_TBD;
+}
+
+// M17Demodulator.h:595-654 up to the decoder call (which decode_kernel performs)
+M17B_FN void do_frame(Scan& z, const LaneIo& e, const Blk& b, int idx /* index() of this sample = pp % 10 */)
+{
+    int diff = z.si - idx;
+    if (diff == 5 || diff == -5) {
+        z.csi = clock_dead_reckon(z.ck_sest, z.ck_est, z.ck_count);
+        z.si = z.csi;
+        return;
+    }
+    if (idx != z.si) return;
+    frame_symbol(z, e, y_sel(b.y, (int) (z.p - b.base)));
 }
 
 M17B_FN bool sw_trig(const Scan& z, int k) { return (z.sw >> (8 * k + 4)) & 1; }
@@ -1200,6 +1243,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                 clocked(z, 1);
                 z.k = z.gap_k;
                 z.mbits = mask_bits(e, z.p);
+                z.have_y8 = false;
                 clock_gate(z, e, i10);
                 do_unlocked(z, e);
                 ++j;
@@ -1224,109 +1268,84 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
             // ---- frame walk: ST_FRAME, M17Demodulator.h:595-654 ---------------------------------
             // Inside a frame only two kinds of sample do anything: the one half a symbol away from the symbol
             // instant (dead-reckoning clock update, which may move sample_index by one) and the symbol instant
-            // itself (slice, soft bits, framer).  The walk goes from event to event by position -- one pass of
-            // the loop = at most one clock update followed by at most one symbol, the order they come in once a
-            // frame is under way, so the lanes of a warp run the same code whatever their symbol phases -- and
-            // feeds the limit filter, which no frame event looks at, whole blocks at a time behind the walk.
+            // itself (slice, soft bits, framer).
             if (defer && head - pos < 1920u &&
                 frame_end_offset(z.si, z.i10, z.framer_index) - kDeferMarginFrame >= (int) (head - pos)) {
                 deferred = true;                            // this frame ends after the head: the next submit's
                 break;
             }
-            const uint32_t pos0 = pos;
-            const uint32_t left = head - pos;
-            const int n = (uint32_t) (960 - z.count) < left ? 960 - z.count : (int) left;
-            uint32_t bqp = pos0;                            // the limit filter has consumed [pos0, bqp)
-            Chunk pfa, pfb;                                 // the blocks at bqp & ~7 and after it
-            load_chunk(pfa, e, bqp & ~7u);
-            load_chunk(pfb, e, (bqp & ~7u) + 8u);
-            int done = 0, i10 = z.i10, si = z.si;
+            // Aligned 8-sample blocks, every lane of the warp one block per pass, from here to the end of the
+            // frame in ONE loop (the carrier-detect cadence, every 960 samples and always at a block end, is
+            // handled inside it), so that the lanes of a warp, which all start their frames in the same pass of
+            // the round, stay together: the limit filter over the block, and the block's events -- at most one
+            // symbol instant and one clock update in nearly every case, in either order -- in fixed slots
+            // (update, symbol, update); anything else falls to the general loop after them.  The symbol's sample
+            // comes from the block in registers; blocks are requested two passes ahead.
+            uint32_t base = pos & ~7u;
+            int jb = (int) (pos - base), done = 0;
+            Chunk c0, c1, c2;
+            load_chunk(c0, e, base); load_chunk(c1, e, base + 8u); load_chunk(c2, e, base + 16u);
+#define M17B_NEXT_EVENTS()                                                                              \
+            do { dd = z.si - z.i10; dd = dd < 0 ? dd + 10 : dd;   /* samples until index() == sample_index */  \
+                 aa = dd >= 5 ? dd - 5 : dd + 5;                  /* ... until |sample_index - index()| == 5 */ \
+            } while (0)
+#define M17B_CLOCK_EVENT()                                                                              \
+            do { j += aa + 1; z.ck_count += (uint32_t) (aa + 1);  /* clock_recovery(sample) on every sample, :712 */ \
+                 z.i10 = z.si >= 4 ? z.si - 4 : z.si + 6;         /* index() of the sample after the one at si + 5 */ \
+                 z.si = clock_dead_reckon(z.ck_sest, z.ck_est, z.ck_count); z.csi = z.si;                     \
+                 M17B_NEXT_EVENTS();                                                                          \
+            } while (0)
+#define M17B_SYMBOL_EVENT()                                                                             \
+            do { j += dd + 1; z.ck_count += (uint32_t) (dd + 1);                                              \
+                 z.i10 = z.si == 9 ? 0 : z.si + 1;                                                            \
+                 frame_symbol(z, e, y_sel(c0.y, j - 1));                                                      \
+                 M17B_NEXT_EVENTS();                                                                          \
+            } while (0)
             for (;;) {
-                int dd = si - i10; dd = dd < 0 ? dd + 10 : dd;                  // samples until index() == sample_index
-                int aa = dd >= 5 ? dd - 5 : dd + 5;                             // ... until |sample_index - index()| == 5
-                float ys = e.ring_y[ring_off(pos0 + (uint32_t) (done + dd), e.lmask, e.np, e.s)];   // requested early
-                if (aa < dd) {
-                    if (aa >= n - done) { z.ck_count += (uint32_t) (n - done); i10 = (i10 + (n - done)) % 10; done = n; break; }
-                    done += aa + 1;
-                    z.ck_count += (uint32_t) (aa + 1);      // clock_recovery(filtered_sample) on every sample, :712
-                    // ClockRecovery.h:76-88 (see do_frame)
-                    const float v = z.ck_sest + z.ck_est * (float) z.ck_count;
-                    const float av = fabsf(v);
-                    float csw;
-                    if (av < 10.f) csw = v;
-                    else if (av < 20.f) csw = v - (v < 0 ? -10.0f : 10.0f);
-                    else csw = (float) fmod((double) v, 10.0);
-                    int r;
-                    if (csw < 0.f) r = (int) (int8_t) round((double) csw + 10.0);
-                    else r = round_half_away(csw);
-                    const int nsi = wrap_index(r);
-                    i10 = si >= 4 ? si - 4 : si + 6;        // index() of the sample after the one at (si + 5) % 10
-                    z.csi = nsi;
-                    if (nsi != si) {
-                        si = nsi;
-                        dd = si - i10; dd = dd < 0 ? dd + 10 : dd;
-                        ys = e.ring_y[ring_off(pos0 + (uint32_t) (done + dd), e.lmask, e.np, e.s)];
-                    } else {
-                        dd = 4;                             // from (si + 6) % 10 to si
-                    }
-                    aa = dd >= 5 ? dd - 5 : dd + 5;
+                const uint32_t left = head - pos;
+                const int je = left < (uint32_t) (8 - jb) ? jb + (int) left : 8;
+                int j = jb, dd, aa;
+                M17B_NEXT_EVENTS();
+                if (aa < dd && j + aa < je) M17B_CLOCK_EVENT();
+                if (dd < aa && j + dd < je) M17B_SYMBOL_EVENT();
+                if (!z.pending && aa < dd && j + aa < je) M17B_CLOCK_EVENT();
+                while (!z.pending && j + (aa < dd ? aa : dd) < je) {
+                    if (aa < dd) M17B_CLOCK_EVENT();
+                    else M17B_SYMBOL_EVENT();
                 }
-                if (aa >= dd) {
-                    if (dd >= n - done) { z.ck_count += (uint32_t) (n - done); i10 = (i10 + (n - done)) % 10; done = n; break; }
-                    done += dd + 1;
-                    z.ck_count += (uint32_t) (dd + 1);
-                    i10 = si == 9 ? 0 : si + 1;
-                    float sample = ys - z.offset;
-                    sample *= z.idev;                       // polarity is +1 and never changes
-                    // SymbolEvm.h:31-51 + StandardDeviation.h:68-72
-                    float err;
-                    if (sample > 2) err = sample - 3;
-                    else if (sample > 0) err = sample - 1;
-                    else if (sample > -2) err = sample + 1;
-                    else err = sample + 3;
-                    const float alpha = (float) (1.0 / 184);
-                    z.evm -= z.evm * alpha;
-                    z.evm += (err * err) * alpha;
-                    const uint32_t pair = llr4(*e.llr_tab, sample);
-                    e.llr[(size_t) (z.framer_index >> 1) * e.np] = (int16_t) pair;      // M17Framer.h:42-53
-                    z.framer_index += 2;
-                    if (z.framer_index == 368) {
-                        z.framer_index = 0;
-                        z.sync_count = 0;
-                        z.pending = true;                   // decoder(...) runs in decode_kernel
-                        z.state = ST_TBD;
+                if (!z.pending) {                           // the rest of the block only counts
+                    z.ck_count += (uint32_t) (je - j);
+                    z.i10 += je - j; z.i10 = z.i10 >= 10 ? z.i10 - 10 : z.i10;
+                    j = je;
+                }
+                bq_feed(z.bq, c0.y, jb, j);
+                done += j - jb;
+                pos += (uint32_t) (j - jb);
+                z.count += j - jb;
+                if (z.count == 960) {                       // :742-752
+                    float l1, l2;
+                    dcd_sums(d, e, pos, head, head64, 960, l1, l2);
+                    update_dcd(z, e);
+                    z.count = 0;
+                    emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), true);
+                    dcd_update(z, l1, l2);
+                    if (!z.dcd) {
+                        z.corr_pos = (z.corr_pos + done) % 80; done = 0;
+                        gate_off(d, e, z.gap_k, pos);
                         break;
                     }
                 }
-                // the limit filter takes the whole blocks behind the walk
-                while (((bqp & ~7u) + 8u) - pos0 <= (uint32_t) done) {
-                    bq_feed(z.bq, pfa.y, (int) (bqp & 7u), 8);
-                    bqp = (bqp & ~7u) + 8u;
-                    pfa = pfb;
-                    load_chunk(pfb, e, bqp + 8u);
-                }
+                if (z.pending || pos == head || z.state != ST_FRAME) break;
+                base += 8u; jb = 0;
+                c0 = c1; c1 = c2;
+                load_chunk(c2, e, base + 16u);
+                if ((base & 31u) == 0u)                     // pull the ring line after the next one into L2
+                    prefetch_l2(e.ring_y + ring_off(base + 64u, e.lmask, e.np, e.s));
             }
-            pos = pos0 + (uint32_t) done;
-            while (((bqp & ~7u) + 8u) - pos0 <= (uint32_t) done) {
-                bq_feed(z.bq, pfa.y, (int) (bqp & 7u), 8);
-                bqp = (bqp & ~7u) + 8u;
-                pfa = pfb;
-                load_chunk(pfb, e, bqp + 8u);
-            }
-            if (bqp != pos) bq_feed(z.bq, pfa.y, (int) (bqp & 7u), (int) (pos - (bqp & ~7u)));
-            z.si = si;
-            z.i10 = i10;
+#undef M17B_NEXT_EVENTS
+#undef M17B_CLOCK_EVENT
+#undef M17B_SYMBOL_EVENT
             z.corr_pos = (z.corr_pos + done) % 80;
-            z.count += done;
-            if (z.count == 960) {                           // :742-752
-                float l1, l2;
-                dcd_sums(d, e, pos, head, head64, 960, l1, l2);
-                update_dcd(z, e);
-                z.count = 0;
-                emit_diag(d, e, z, head64 - (unsigned long long) (head - pos), true);
-                dcd_update(z, l1, l2);
-                if (!z.dcd) gate_off(d, e, z.gap_k, pos);
-            }
             continue;
         }
 
@@ -1382,6 +1401,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                     clocked(z, 1);
                     z.k = z.gap_k;
                     z.have_limit = false;
+                    z.have_y8 = false;
                     event_step(z, e, b, i10);
                     ++j;
                     if (z.pending || z.state == ST_UNLOCKED) break;
@@ -1431,7 +1451,6 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
          (z.dcd ? FL_DCD : 0) | (z.dcd_trig ? FL_DCD_TRIG : 0) | (z.need_reset ? FL_NEED_RESET : 0) |
          (z.need_update ? FL_NEED_UPDATE : 0) | (z.dev_reset ? FL_DEV_RESET : 0) | (z.eot ? FL_EOT : 0) |
          (z.pending ? FL_PENDING : 0) | (fixup ? FL_FIXUP : 0);
-    sb[F_FLAGS * 32] = fl;
     sb[F_GAPR * 32] = gap_r;
     sb[F_GAPDONE * 32] = (uint32_t) gap_done;
     sb[F_SYNC_COUNT * 32] = (uint32_t) z.sync_count; sb[F_MISSING * 32] = (uint32_t) z.missing;
@@ -1439,7 +1458,12 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     // the searched span only means something while the search that asked for it goes on
     if (!(z.state == ST_UNLOCKED && z.dcd && !z.init)) sfrom = sto = pos;
     sb[F_SFROM * 32] = sfrom; sb[F_STO * 32] = sto;
-    if (fixup) d.fix_list[ctr_add(&d.ctr->fix_count, 1u)] = e.s;
+    // The flags word goes last, behind a fence: it is what classify_kernel goes by, and a round of the receiving
+    // streams may be classified while the acquiring streams' chain of an earlier round is still running (run_round) --
+    // whoever sees flags that make the stream its own must see the rest of the state as well.
+    publish_fence();
+    sb[F_FLAGS * 32] = fl;
+    if (fixup) d.fix_list[(size_t) e.cls * d.np + ctr_add(&d.ctr->cls[e.cls].fix_count, 1u)] = e.s;
     if (z.pending) {
         // queue the frame by what M17FrameDecoder::operator() will do with it (M17FrameDecoder.h:353-392),
         // so that decode_kernel's warps each run one kind
@@ -1449,7 +1473,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
         else if (z.swt == SW_BERT) kind = 3;
         else if (z.swt == SW_STREAM) { if (dec_state == DEC_STREAM) kind = 1; }
         else if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) kind = 2;
-        d.dec_list[(size_t) kind * d.np + ctr_add(&d.ctr->dec_count[kind], 1u)] = e.s;
+        d.dec_list[(size_t) (e.cls * 5 + kind) * d.np + ctr_add(&d.ctr->cls[e.cls].dec_count[kind], 1u)] = e.s;
     }
     if (deferred) ctr_add(&d.ctr->deferred, 1u);
     else if (pos != head) ctr_add(&d.ctr->lagging, 1u);
@@ -1471,9 +1495,10 @@ M17B_FN void init_lane(uint32_t* sb, uint32_t pos0 = 0)
     sb[F_POS * 32] = pos0; sb[F_GAPR * 32] = pos0; sb[F_SFROM * 32] = pos0; sb[F_STO * 32] = pos0;
 }
 
-M17B_FN LaneIo make_io(const DevPtrs& d, uint32_t s, const LlrTable* tab)
+M17B_FN LaneIo make_io(const DevPtrs& d, uint32_t s, const LlrTable* tab, int cls = 0)
 {
     LaneIo e;
+    e.cls = cls;
     e.llr_tab = tab;
     e.sb = d.st + st_index(s, 0);
     e.sw_samples = d.sw_samples + s;
@@ -1945,6 +1970,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
         }
     }
     fl = (fl & ~(7u << FL_STATE_SHIFT) & ~FL_PENDING) | ((uint32_t) state << FL_STATE_SHIFT);
+    publish_fence();                                        // see scan_lane's write-back
     sb[F_FLAGS * 32] = fl;
 }
 

@@ -56,7 +56,7 @@ class Profile(ctypes.Structure):
                 ("d2h_ms", ctypes.c_double), ("d2h_bytes", ctypes.c_uint64),
                 ("dcd_ms", ctypes.c_double), ("dcd_launches", ctypes.c_uint64),
                 ("fixup_ms", ctypes.c_double), ("fixup_launches", ctypes.c_uint64),
-                ("search_requests", ctypes.c_uint64), ("search_samples", ctypes.c_uint64)]
+                ("search_requests", ctypes.c_uint64), ("search_samples", ctypes.c_uint64), ("scan1_ms", ctypes.c_double)]
 
 
 _lib = None

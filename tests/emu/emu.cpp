@@ -88,8 +88,8 @@ void round(Emu& m, bool defer)
     DevPtrs& d = m.d;
     m.ctr.lagging = 0;
     m.ctr.deferred = 0;
-    m.ctr.fix_count = 0;
-    for (int k = 0; k != 5; ++k) m.ctr.dec_count[k] = 0;
+    m.ctr.cls[0].fix_count = 0;
+    for (int k = 0; k != 5; ++k) m.ctr.cls[0].dec_count[k] = 0;
     for (uint32_t s = 0; s != d.n_streams; ++s) scan_lane(d, make_io(d, s, &m.tab), m.head, m.head64, true, defer);
     if (const char* t = getenv("M17EMU_TRACE")) {
         const uint32_t s = (uint32_t) atoi(t);
@@ -103,8 +103,8 @@ void round(Emu& m, bool defer)
     }
     uint16_t hist[244];
     for (int k = 0; k != 5; ++k)
-        for (uint32_t q = 0; q != m.ctr.dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) k * d.np + q], hist, m.head, m.head64);
-    for (uint32_t q = 0; q != m.ctr.fix_count; ++q) {
+        for (uint32_t q = 0; q != m.ctr.cls[0].dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) k * d.np + q], hist, m.head, m.head64);
+    for (uint32_t q = 0; q != m.ctr.cls[0].fix_count; ++q) {
         const uint32_t s = m.fix_list[q];
         fixup_lane(d, s, m.head);
         search_lane(d, s, m.head);

@@ -234,14 +234,17 @@ def test_streaming_mode_whole_frame_deferral(chunk):
     x = gen.generate(random_params(21, gen.MIXED, 96), n)
     want, _ = ol.demod_batch("port", x)
     with m.Demodulator(96, 9600, flags=m.STREAMING) as d:
-        parts, prev, ends = [], None, []
+        parts, prev, late, n_rec = [], None, 0, 0
         for o in range(0, n, chunk):
             d.submit(np.ascontiguousarray(x[:, o:o + chunk]))
             t = d.ticket()
             if prev is not None:
                 r = d.drain_upto(prev[0])
-                # delivered with its own submit: nothing older than the previous submit's first sample
-                assert len(r) == 0 or int(r["sample_pos"].min()) >= prev[1]
+                # a receiving stream delivers every frame with the submit it ends in; one that is acquiring (start of
+                # a transmission: the acquiring streams get fewer rounds per submit) may trail by up to two more submits
+                assert len(r) == 0 or int(r["sample_pos"].min()) >= prev[1] - 2 * chunk
+                late += int((r["sample_pos"] < prev[1]).sum())
+                n_rec += len(r)
                 parts.append(r)
             prev = (t, o)
         parts.append(d.drain())
@@ -249,6 +252,7 @@ def test_streaming_mode_whole_frame_deferral(chunk):
         got = m.demod.split_by_stream(np.concatenate(parts), 96)
     assert c.faults == 0 and c.dropped == 0
     assert_records_match(want, got, f"streaming chunk {chunk}")
+    assert late <= n_rec // 4, f"{late} of {n_rec} records arrived after their own submit"
 
 
 def _crc_x25(data: bytes) -> int:
