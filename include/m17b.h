@@ -60,8 +60,8 @@ extern "C" {
                                 * stream may trail the newest sample, so that it always walks whole frames.
                                 * A stream that is receiving delivers every frame that ends inside a submit
                                 * with that submit; one that is acquiring (idle, searching for sync words, in
-                                * a preamble) is served at a lower rate and may deliver up to two submits
-                                * later.  m17b_sync / m17b_drain bring all streams up to the newest sample
+                                * a preamble) is served at its own pace and may deliver up to two submits
+                                * (of max_chunk samples) later; the sample ring holds four.  m17b_sync / m17b_drain bring all streams up to the newest sample
                                 * first (their diagnostics then match the reference's).  */
 
 #define M17B_DIAG_RECORDS 0x10u /* record one m17b_diag_rec per reference diagnostic callback (m17b_diag_drain);

@@ -44,7 +44,7 @@ struct m17b_ctx {
     cudaStream_t front = nullptr;
     cudaStream_t aux = nullptr;                // chain of walk class 1 of a round (run_round)
     cudaEvent_t ev_cls = nullptr, ev_aux = nullptr;
-    bool aux_running = false;                  // an aux chain has been enqueued that `compute` has not waited for yet
+    cudaEvent_t ev_aux_rounds[2] = {nullptr, nullptr};   // M17B_STREAMING: aux chain of submit k done (like ev_rounds)
     cudaEvent_t ev_front = nullptr, ev_rounds[2] = {nullptr, nullptr};
     unsigned long long n_submits = 0;
     uint32_t head = 0;
@@ -123,50 +123,55 @@ void ev_collect(m17b_ctx* c)
     c->ev_live.clear();
 }
 
-// One round: every stream that has samples to walk advances to its next completed frame (or until it needs
-// fixup_kernel), the completed frames are decoded, the fix-up / search requests served.  The streams are sorted
-// into two walk classes first (classify_kernel) and each class runs its own chain scan -> decode -> fix-up: the
-// receiving streams (class 0) on `st`, the acquiring ones (class 1: idle, start-up, sync-word search, preamble)
-// on the aux stream beside it.  The acquiring streams are few, but theirs are long serial walks -- a round of them
-// takes as long as two or three rounds of the receiving streams -- so with `with_aux` clear a round lists the
-// receiving streams only and leaves the aux chain of an earlier round running; the flags word of a stream is
-// what hands it from one chain to the other (see scan_lane's write-back).  `wait_end`: the round ends when both
-// chains have.
-int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard, bool with_aux, bool wait_end)
+// One round of one chain: the streams of the walk classes in `mask` that have samples to walk (classify_kernel)
+// advance to their next completed frame (or until they need fixup_kernel), the completed frames are decoded, the
+// fix-up / search requests served.  Class 0 = receiving streams, class 1 = acquiring ones (idle, start-up,
+// sync-word search, preamble): few, but theirs are long serial walks.
+//   mask 3 (m17b_sync's flush rounds, contexts without M17B_STREAMING): one classification on `st`, class 1's chain
+//          forked to the aux stream beside class 0's, the round ends when both have;
+//   mask 1 / 2 (M17B_STREAMING): the chain of one class alone on `st`.  The two chains of a submit then run
+//          independently (m17b_submit), each classifying for itself: the flags word of a stream says whose it is,
+//          and it is published last (scan_lane's write-back, decode_lane, fixup_done_kernel).
+int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard, uint32_t mask)
 {
     EvPair p{};
-    if (with_aux && c->aux_running) { CK(cudaStreamWaitEvent(st, c->ev_aux, 0)); c->aux_running = false; }
-    // lagging, deferred and the work lists of the classes this round runs
-    CK(cudaMemsetAsync(&c->d.ctr->lagging, 0, 2 * sizeof(unsigned int) + (with_aux ? 2 : 1) * sizeof(ClassCounters), st));
-    launch_classify(c->d, c->head, with_aux ? 3u : 1u, st);
-    if (with_aux) {
+    const int first = (mask & 1u) ? 0 : 1, last = (mask & 2u) ? 1 : 0;
+    CK(cudaMemsetAsync(&c->d.ctr->cls[first], 0, (size_t) (last - first + 1) * sizeof(ClassCounters), st));
+    launch_classify(c->d, c->head, mask, defer, st);
+    const bool fork = mask == 3u;
+    if (fork) {
         CK(cudaEventRecord(c->ev_cls, st));
         CK(cudaStreamWaitEvent(c->aux, c->ev_cls, 0));
     }
-    for (int cls = with_aux ? 1 : 0; cls >= 0; --cls) {
-        cudaStream_t s = cls ? c->aux : st;
+    for (int cls = last; cls >= first; --cls) {
+        cudaStream_t s = (fork && cls) ? c->aux : st;
         ev_begin(c, s, cls ? CAT_SCAN1 : CAT_SCAN, p);
-        launch_scan(c->d, c->head, c->head64, defer, guard, cls, s);
+        launch_scan(c->d, c->head, c->head64, defer, guard, cls, mask == 2u, s);
         ev_end(c, s, p);
         ev_begin(c, s, CAT_DECODE, p);
         launch_decode(c->d, c->head, c->head64, cls, s);
         ev_end(c, s, p);
-        ev_begin(c, s, CAT_FIXUP, p);
-        launch_fixup(c->d, c->head, c->sm_count, cls, s);
-        ev_end(c, s, p);
-        if (cls) { CK(cudaEventRecord(c->ev_aux, s)); c->aux_running = true; }
+        if (cls) {                   // (a receiving stream that needs fixup_kernel becomes class 1 first, see scan_lane)
+            ev_begin(c, s, CAT_FIXUP, p);
+            launch_fixup(c->d, c->head, c->sm_count, cls, s);
+            ev_end(c, s, p);
+            c->prof.fixup_launches += 4;
+        }
         c->prof.scan_launches += 1;
         c->prof.decode_launches += 1;
-        c->prof.fixup_launches += 3;
     }
     c->prof.scan_launches += 1;      // classify_kernel
-    if (wait_end && c->aux_running) { CK(cudaStreamWaitEvent(st, c->ev_aux, 0)); c->aux_running = false; }
+    if (fork) {
+        CK(cudaEventRecord(c->ev_aux, c->aux));
+        CK(cudaStreamWaitEvent(st, c->ev_aux, 0));
+    }
     CK(cudaGetLastError());
     return M17B_OK;
 }
 
 int fetch_counters(m17b_ctx* c)
 {
+    CK(cudaStreamSynchronize(c->aux));                       // the acquiring streams' chain (M17B_STREAMING) has its own stream
     CK(cudaMemcpyAsync(&c->host_ctr, c->d.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->compute));
     CK(cudaStreamSynchronize(c->compute));
     return M17B_OK;
@@ -238,6 +243,7 @@ void free_all(m17b_ctx* c)
     if (c->aux) cudaStreamDestroy(c->aux);
     if (c->ev_cls) cudaEventDestroy(c->ev_cls);
     if (c->ev_aux) cudaEventDestroy(c->ev_aux);
+    for (auto& e : c->ev_aux_rounds) if (e) cudaEventDestroy(e);
     if (c->ev_front) cudaEventDestroy(c->ev_front);
     for (auto& e : c->ev_rounds) if (e) cudaEventDestroy(e);
     delete c;
@@ -298,6 +304,7 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
             CK(cudaStreamCreateWithPriority(&c->aux, cudaStreamNonBlocking, prio_hi));
             CK(cudaEventCreateWithFlags(&c->ev_cls, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming));
+            for (auto& e : c->ev_aux_rounds) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&c->ev_front, cudaEventDisableTiming));
             for (auto& e : c->ev_rounds) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
@@ -311,7 +318,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         // of the slow filter path / sliding DFT
         // M17B_STREAMING: the next submit's filter writes its chunk while the lanes of this one are still
         // running their rounds (front stream), so a lane may be a whole chunk further behind the newest ring write
-        uint32_t need = cfg->max_chunk * ((cfg->flags & M17B_STREAMING) ? 2u : 1u) + kRoundCap + 160 + 16;
+        // (... and an acquiring stream is served by a chain of its own, at its own pace, and changes chains a few times
+        // on its way into a transmission: it may trail the head by up to two more submits, hence four in all)
+        uint32_t need = cfg->max_chunk * ((cfg->flags & M17B_STREAMING) ? 4u : 1u) + kRoundCap + 160 + 16;
         d.ring_lines = next_pow2((need + kLine - 1) / kLine + 1);
         // at most 2 callbacks (LICH + LSF) per completed frame, completions >= kMinFrameSpacing apart; room for
         // three submits: the one being drained and two enqueued behind it (m17b_drain_upto pipelines of depth <= 2;
@@ -438,8 +447,12 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     // doubled it writes no ring position a lane of the previous submit still reads (ring guard in scan_lane).
     // It may be one submit ahead of the rounds, not two.
     const bool streaming = (c->cfg.flags & M17B_STREAMING) != 0;
-    cudaStream_t fs = streaming ? c->front : c->compute;
-    if (streaming) CK(cudaStreamWaitEvent(fs, c->ev_rounds[c->n_submits & 1], 0));     // rounds of submit k-2
+    static const bool no_front = getenv("M17B_NO_FRONT") != nullptr;      // experiment: front end in line with the rounds
+    cudaStream_t fs = streaming && !no_front ? c->front : c->compute;
+    if (streaming) {                                                                    // rounds of submit k-2, both chains
+        CK(cudaStreamWaitEvent(fs, c->ev_rounds[c->n_submits & 1], 0));
+        CK(cudaStreamWaitEvent(fs, c->ev_aux_rounds[c->n_submits & 1], 0));
+    }
     if (location == M17B_HOST) {
         int b = c->cur_stage;
         c->cur_stage ^= 1;
@@ -476,6 +489,7 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     if (streaming) {
         CK(cudaEventRecord(c->ev_front, fs));
         CK(cudaStreamWaitEvent(c->compute, c->ev_front, 0));
+        CK(cudaStreamWaitEvent(c->aux, c->ev_front, 0));
     }
     CK(cudaGetLastError());
     c->cur_tail ^= 1;
@@ -495,12 +509,27 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     // rounds let stragglers (acquisition, carrier-detect gaps, fix-ups) catch up.  A round costs a frame's
     // worth of serial latency however few lanes run; the next submit's front end fills the machine meanwhile.
     const int rounds = (int) (n / kMinFrameSpacing) + 2;
-    for (int r = 0; r != rounds; ++r) {
-        // M17B_STREAMING: the acquiring streams get every third round (their rounds are long, and they may trail the
-        // head by more than a submit: the ring is doubled); otherwise every round, so that all streams reach the head
-        const bool with_aux = !streaming || r % 3 == 0;
-        int rc = run_round(c, streaming, c->compute, streaming ? c->cfg.max_chunk : 0u, with_aux, !streaming || r == rounds - 1);
-        if (rc != M17B_OK) return rc;
+    if (streaming) {
+        // two independent chains: the receiving streams' rounds on `compute`, the acquiring streams' on `aux`.  An
+        // acquiring stream's round is a long serial walk (a preamble, a search span, then a frame) and there are few
+        // such streams, so they get about half as many rounds, run beside the others; they may trail the head by
+        // more than a submit meanwhile (the ring is doubled; `faults` guards it).
+        const uint32_t guard = c->cfg.max_chunk;
+        for (int r = 0; r != rounds; ++r) {
+            int rc = run_round(c, true, c->compute, guard, 1u);
+            if (rc != M17B_OK) return rc;
+        }
+        static const int aux_rounds = getenv("M17B_AUX_ROUNDS") ? atoi(getenv("M17B_AUX_ROUNDS")) : 0;     // experiment
+        for (int r = 0; r != (aux_rounds ? aux_rounds : rounds); ++r) {
+            int rc = run_round(c, true, c->aux, guard, 2u);
+            if (rc != M17B_OK) return rc;
+        }
+        CK(cudaEventRecord(c->ev_aux_rounds[c->n_submits & 1], c->aux));
+    } else {
+        for (int r = 0; r != rounds; ++r) {
+            int rc = run_round(c, false, c->compute, 0u, 3u);
+            if (rc != M17B_OK) return rc;
+        }
     }
     if (streaming) CK(cudaEventRecord(c->ev_rounds[c->n_submits & 1], c->compute));
     c->n_submits += 1;
@@ -519,9 +548,10 @@ int m17b_sync(m17b_ctx* c)
     CK(cudaSetDevice(c->cfg.device));
     int rc = fetch_counters(c);
     if (rc != M17B_OK) return rc;
-    for (int extra = 0; c->host_ctr.lagging != 0 || c->host_ctr.deferred != 0; ++extra) {
+    auto behind = [&] { return c->host_ctr.cls[0].lagging | c->host_ctr.cls[0].deferred | c->host_ctr.cls[1].lagging | c->host_ctr.cls[1].deferred; };
+    for (int extra = 0; behind() != 0; ++extra) {
         if (extra == 256) { c->last_error = "streams failed to reach the head"; return M17B_ESTATE; }
-        if ((rc = run_round(c, false, c->compute, 0, true, true)) != M17B_OK) return rc;
+        if ((rc = run_round(c, false, c->compute, 0u, 3u)) != M17B_OK) return rc;
         if ((rc = fetch_counters(c)) != M17B_OK) return rc;
     }
     ev_collect(c);

@@ -99,6 +99,8 @@ struct ClassCounters {            // work lists of one walk class, reset before 
     unsigned int scan_count;      // entries in scan_list
     unsigned int fix_count;       // entries in fix_list
     unsigned int dec_count[5];    // entries in dec_list per decode kind
+    unsigned int lagging;         // streams of the class that have not reached the head
+    unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING)
     unsigned int pad;
 };
 
@@ -110,8 +112,6 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned long long dropped;
     unsigned int rec_count;       // record cursor: records appended so far (monotonic, mod 2^32)
     unsigned int diag_count;      // diagnostic-record cursor (M17B_DIAG_RECORDS), monotonic like rec_count
-    unsigned int lagging;         // streams that have not reached head (reset before every round)
-    unsigned int deferred;        // streams that left a partial frame for the next submit (M17B_STREAMING; reset likewise)
     ClassCounters cls[kClasses];
     unsigned long long diag_dropped;
     unsigned long long search_requests;   // sync-word searches served by search_mask_kernel
@@ -182,8 +182,8 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
 void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
-void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, cudaStream_t s);
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, cudaStream_t s);
+void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, bool defer, cudaStream_t s);
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, bool split, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, int cls, cudaStream_t s);
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, int cls, cudaStream_t s);
 void launch_gather(const DevPtrs& d, uint32_t n, float* y, float* x, cudaStream_t s);

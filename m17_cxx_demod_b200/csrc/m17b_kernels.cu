@@ -312,11 +312,11 @@ void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned lo
 // and scan_kernel's warps each take 32 entries of ONE list (per-stream state is then gathered rather than
 // coalesced: a few hundred bytes per stream and round).
 __global__ void __launch_bounds__(256)
-classify_kernel(DevPtrs d, uint32_t head, uint32_t class_mask /* bit c: list class c this round */)
+classify_kernel(DevPtrs d, uint32_t head, uint32_t class_mask /* bit c: list class c this round */, int defer)
 {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     int cls = -1;
-    bool lag = false;
+    bool lag = false, dfr = false;
     if (s < d.n_streams) {
         const volatile uint32_t* sb = d.st + st_index(s, 0);
         // the flags word first: a stream whose flags make it this round's is complete (scan_lane / decode_lane
@@ -324,14 +324,15 @@ classify_kernel(DevPtrs d, uint32_t head, uint32_t class_mask /* bit c: list cla
         const uint32_t fl = sb[F_FLAGS * 32];
         __threadfence();
         const uint32_t pos = sb[F_POS * 32];
-        if (pos != head) {
+        if ((int32_t) (head - pos) > 0) {                       // (a stream may be past this chain's head: the other chain's rounds may belong to a later submit)
             if (fl & (FL_PENDING | FL_FIXUP)) lag = true;       // waits for decode_kernel / fixup_kernel: not at the head yet
             else {
                 const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
                 const bool receiving = (fl & FL_DCD) && (sb[F_CNT * 32] >> 16) == 0 && (sb[F_IDX * 32] >> 24) >= (uint32_t) kTapsUsed &&
                                        (st == ST_FRAME || st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT);
                 cls = receiving ? 0 : 1;
-                if (!((class_mask >> cls) & 1u)) { cls = -1; lag = true; }     // its class sits this round out
+                if (!((class_mask >> cls) & 1u)) cls = -1;      // the other chain's
+                else if (defer && defers_at_once(sb, fl, pos, head)) { cls = -1; dfr = true; }
             }
         }
     }
@@ -346,13 +347,15 @@ classify_kernel(DevPtrs d, uint32_t head, uint32_t class_mask /* bit c: list cla
             if (cls == c) d.scan_list[(size_t) c * d.np + base + (uint32_t) __popc(m & ((1u << lane) - 1u))] = s;
         }
     }
+    const uint32_t md = __ballot_sync(0xFFFFFFFFu, dfr);
+    if (md && lane == 0) atomicAdd(&d.ctr->cls[(class_mask & 1u) ? 0 : 1].deferred, (unsigned) __popc(md));
     const uint32_t ml = __ballot_sync(0xFFFFFFFFu, lag);
-    if (ml && lane == 0) atomicAdd(&d.ctr->lagging, (unsigned) __popc(ml));
+    if (ml && lane == 0) atomicAdd(&d.ctr->cls[(class_mask & 1u) ? 0 : 1].lagging, (unsigned) __popc(ml));
 }
 
-void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, cudaStream_t s)
+void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, bool defer, cudaStream_t s)
 {
-    classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head, class_mask);
+    classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head, class_mask, defer ? 1 : 0);
 }
 
 // The acquiring streams (class 1) are few and each is in a different part of the state machine: 32 of them in
@@ -362,7 +365,7 @@ void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, cudaS
 constexpr int kSpread = 1;
 
 __global__ void __launch_bounds__(kScanThreads)
-scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls)
+scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls, int split)
 {
     __shared__ LlrTable tab;                               // lanes look up different entries: shared, not constant memory
     const int tid = threadIdx.x;
@@ -378,12 +381,12 @@ scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint
     __syncthreads();
     if (g >= n || t % spread != 0) return;
     const uint32_t s = d.scan_list[(size_t) cls * d.np + g];
-    scan_lane(d, make_io(d, s, &tab, cls), head, head64, true, defer != 0, guard);
+    scan_lane(d, make_io(d, s, &tab, cls, split != 0), head, head64, true, defer != 0, guard);
 }
 
-void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, cudaStream_t s)
+void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, bool split, cudaStream_t s)
 {
-    scan_kernel<<<d.np / kScanThreads * (cls ? kSpread : 1), kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard, cls);
+    scan_kernel<<<d.np / kScanThreads * (cls ? kSpread : 1), kScanThreads, 0, s>>>(d, head, head64, defer ? 1 : 0, guard, cls, split ? 1 : 0);
 }
 
 // Thread g takes the g-th entry of the per-kind lists the scan kernel filled, each list padded to
@@ -472,28 +475,41 @@ search_limit_kernel(DevPtrs d, uint32_t head, int cls)
     head = search_end(from, head);
     Biquad b;
     b.h1 = u2f(sb[F_IIR0 * 32]); b.h2 = u2f(sb[F_IIR1 * 32]);
-    // blocks from the one that contains `from`; the next block's samples are requested a block of arithmetic ahead
-    // and the ring line after that is pulled into L2
-    uint32_t base = from & ~7u;
-    const float4* py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base, lmask, d.np, s));
-    float4 a0 = py[0], a1 = py[1];
-    for (; (int32_t) (head - base) > 0; base += 8u) {
-        const float y[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-        py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base + 8u, lmask, d.np, s));
-        a0 = py[0]; a1 = py[1];
-        if ((base & 31u) == 0u)
+    // whole ring lines (32 samples = four blocks) from the one that contains `from`; the next line is requested while
+    // this one's 32 filter steps run, the one after that is pulled into L2 (the recurrence is ~12 dependent cycles per
+    // sample, a line's worth of it about as long as an L2 round trip)
+    uint32_t base = from & ~31u;
+    float4 cur[8], nxt[8];
+    {
+        const float4* py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base, lmask, d.np, s));
+#pragma unroll
+        for (int i = 0; i != 8; ++i) cur[i] = py[i];
+    }
+    for (; (int32_t) (head - base) > 0; base += 32u) {
+        {
+            const float4* py = reinterpret_cast<const float4*>(d.ring_y + ring_off(base + 32u, lmask, d.np, s));
+#pragma unroll
+            for (int i = 0; i != 8; ++i) nxt[i] = py[i];
             asm volatile("prefetch.global.L2 [%0];" :: "l"(d.ring_y + ring_off(base + 96u, lmask, d.np, s)));
-        const uint32_t left = head - base;
-        if ((int32_t) (base - from) >= 0 && left >= 8u) {
-#pragma unroll
-            for (int j = 0; j != 8; ++j) limit_step(b, y[j]);
-            d.ckpt_ring[blk_off(base, lmask, d.np, s)] = make_float2(b.h1, b.h2);
-        } else {
-#pragma unroll
-            for (int j = 0; j != 8; ++j)
-                if ((int32_t) (base + (uint32_t) j - from) >= 0 && (uint32_t) j < left) limit_step(b, y[j]);
-            if (left >= 8u) d.ckpt_ring[blk_off(base, lmask, d.np, s)] = make_float2(b.h1, b.h2);
         }
+#pragma unroll
+        for (int k = 0; k != 4; ++k) {
+            const uint32_t b8 = base + 8u * (uint32_t) k;
+            if ((int32_t) (b8 + 8u - from) <= 0 || (int32_t) (head - b8) <= 0) continue;     // before the span / past its end
+            const float y[8] = {cur[2 * k].x, cur[2 * k].y, cur[2 * k].z, cur[2 * k].w, cur[2 * k + 1].x, cur[2 * k + 1].y, cur[2 * k + 1].z, cur[2 * k + 1].w};
+            const uint32_t left = head - b8;
+            if ((int32_t) (b8 - from) >= 0 && left >= 8u) {
+#pragma unroll
+                for (int j = 0; j != 8; ++j) limit_step(b, y[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j != 8; ++j)
+                    if ((int32_t) (b8 + (uint32_t) j - from) >= 0 && (uint32_t) j < left) limit_step(b, y[j]);
+            }
+            if (left >= 8u) d.ckpt_ring[blk_off(b8, lmask, d.np, s)] = make_float2(b.h1, b.h2);
+        }
+#pragma unroll
+        for (int i = 0; i != 8; ++i) cur[i] = nxt[i];
     }
 }
 
@@ -564,23 +580,32 @@ search_mask_kernel(DevPtrs d, uint32_t head_all, int cls)
                 d.mask_ring[blk_off(base, lmask, d.np, s)] = word;
             }
         }
-        if (first) {
-            if (search) {
-                sb[F_SFROM * 32] = sb[F_POS * 32]; sb[F_STO * 32] = head;
-                atomicAdd(&d.ctr->search_requests, 1ull);
-                atomicAdd(&d.ctr->search_samples, (unsigned long long) (head - sb[F_POS * 32]));
-            }
-            sb[F_FLAGS * 32] &= ~FL_FIXUP;
+        if (first && search) {
+            sb[F_SFROM * 32] = sb[F_POS * 32]; sb[F_STO * 32] = head;
+            atomicAdd(&d.ctr->search_requests, 1ull);
+            atomicAdd(&d.ctr->search_samples, (unsigned long long) (head - sb[F_POS * 32]));
         }
     }
+}
+
+// The requests are served: the streams may be walked again.  Its own launch, behind the kernels above: the flags
+// word is what hands a stream to whichever chain classifies it next, so everything else must be in place first.
+__global__ void __launch_bounds__(128)
+fixup_done_kernel(DevPtrs d, int cls)
+{
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= d.ctr->cls[cls].fix_count) return;
+    uint32_t* sb = d.st + st_index(d.fix_list[(size_t) cls * d.np + q], 0);
+    sb[F_FLAGS * 32] &= ~FL_FIXUP;
 }
 
 void launch_fixup(const DevPtrs& d, uint32_t head, int sm_count, int cls, cudaStream_t s)
 {
     fixup_kernel<<<sm_count * 8, kFixThreads, 0, s>>>(d, head, cls);
     search_limit_kernel<<<d.np / 128, 128, 0, s>>>(d, head, cls);
-    // a request's span is at most kSearchSpan + 7 samples: x = its blocks, y = requests in strides of the grid
-    search_mask_kernel<<<dim3(2, (unsigned) sm_count * 4), kMaskThreads, 0, s>>>(d, head, cls);
+    // a request's span is at most kSearchSpan + 7 samples (one pass of x = its blocks), y = requests in strides of the grid
+    search_mask_kernel<<<dim3(4, (unsigned) sm_count * 2), kMaskThreads, 0, s>>>(d, head, cls);
+    fixup_done_kernel<<<d.np / 128, 128, 0, s>>>(d, cls);
 }
 
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, int cls, cudaStream_t s)

@@ -201,6 +201,7 @@ struct LaneIo {
     const float2* ckpt_ring;
     uint32_t np, lmask, s;
     int cls;               // walk class the lane was listed in (selects the work lists it appends to)
+    bool split;            // M17B_STREAMING: the two classes have a chain of rounds each (m17b_submit), and this is the acquiring streams'
 };
 
 M17B_FN size_t ring_off(uint32_t p, uint32_t lmask, uint32_t np, uint32_t s)
@@ -1027,6 +1028,7 @@ M17B_FN void dcd_sums(const DevPtrs& d, const LaneIo& e, uint32_t pos, uint32_t 
 // Offset, from the next sample the lane handles (logical slot corr_pos), of the last symbol instant of
 // the frame being received (ST_FRAME): symbols are taken when index() == sample_index, 10 samples apart
 // (the dead-reckoned sample_index moves by at most +-1 a few times per frame).
+constexpr int kWalkBudget = 768;         // samples of block walk per round of an acquiring stream (M17B_STREAMING)
 constexpr int kDeferMarginFrame = 6;
 constexpr int kDeferMarginSync = 16;
 M17B_FN int frame_end_offset(int si, int i10, int framer_index)
@@ -1118,6 +1120,24 @@ M17B_FN void emit_diag(const DevPtrs& d, const LaneIo& e, const Scan& z, unsigne
     emit_diag_rec(d, e.s, v);
 }
 
+// M17B_STREAMING: would scan_lane leave this stream where it is, because the frame it is in (or waiting for) cannot
+// complete before the head?  (classify_kernel asks too, so that such streams take no lane of a round.)
+template <typename P>
+M17B_FN bool defers_at_once(const P* sb, uint32_t fl, uint32_t pos, uint32_t head)
+{
+    const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
+    const long long left = (long long) (head - pos);
+    if (st == ST_FRAME) {
+        const uint32_t idx = sb[F_IDX * 32];
+        const int eo = frame_end_offset((int) ((fl >> FL_SI_SHIFT) & 15), (int) (idx & 0xFF) % 10, (int) ((idx >> 8) & 0xFFFF));
+        return (long long) eo - kDeferMarginFrame >= left;
+    }
+    if (st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT)
+        // sync_count counts samples from the last frame's end; frames are 1920 samples apart
+        return 1919ll - (long long) sb[F_SYNC_COUNT * 32] - kDeferMarginSync >= left;
+    return false;
+}
+
 // Walk this lane from its position towards `head`; on return the lane is at head, stopped on a completed
 // frame (FL_PENDING, decode_kernel's turn), waiting for fixup_kernel (FL_FIXUP: matched-filter outputs after a
 // carrier-detect gap and / or a sync-word search over the samples ahead), or has left a partial frame for
@@ -1136,8 +1156,8 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     uint32_t* sb = e.sb;
     uint32_t pos = sb[F_POS * 32];
     uint32_t fl = sb[F_FLAGS * 32];
-    if (pos == head) return;
-    if (fl & (FL_PENDING | FL_FIXUP)) { ctr_add(&d.ctr->lagging, 1u); return; }
+    if ((int32_t) (head - pos) <= 0) return;               // at the head -- or past it: the other chain's rounds may belong to a later submit
+    if (fl & (FL_PENDING | FL_FIXUP)) { ctr_add(&d.ctr->cls[e.cls].lagging, 1u); return; }
     // Deferral (rounds enqueued by m17b_submit; m17b_sync's flush rounds run every lane to the head): a lane
     // whose current frame cannot complete before the head leaves the rest of the chunk for the next submit.
     // The records are the same -- every frame that ends inside this chunk is still completed here -- but the
@@ -1147,20 +1167,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     // the next sync word is awaited, only to -11 .. +5 (a re-timed sync word moves the symbol phase), hence
     // the wider margin there -- a lane inside that margin starts walking and is stopped by the same test a
     // few blocks later, once it is in ST_FRAME (block walk below).
-    if (defer) {
-        const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
-        const long long left = (long long) (head - pos);
-        bool deferred = false;
-        if (st == ST_FRAME) {
-            const uint32_t idx = sb[F_IDX * 32];
-            const int eo = frame_end_offset((int) ((fl >> FL_SI_SHIFT) & 15), (int) (idx & 0xFF) % 10, (int) ((idx >> 8) & 0xFFFF));
-            if ((long long) eo - kDeferMarginFrame >= left) deferred = true;
-        } else if (st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT) {
-            // sync_count counts samples from the last frame's end; frames are 1920 samples apart
-            if (1919ll - (long long) sb[F_SYNC_COUNT * 32] - kDeferMarginSync >= left) deferred = true;
-        }
-        if (deferred) { ctr_add(&d.ctr->deferred, 1u); return; }
-    }
+    if (defer && defers_at_once(sb, fl, pos, head)) { ctr_add(&d.ctr->cls[e.cls].deferred, 1u); return; }
     // a stream that fell so far behind that the sample ring has wrapped over what it still needs
     // (submits enqueued back to back without m17b_sync and more stops than rounds): must never happen
     if (head + guard - pos > d.ring_lines * (uint32_t) kLine - 176u) ctr_add(&d.ctr->faults, 1ull);
@@ -1168,7 +1175,13 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     uint32_t gap_r = sb[F_GAPR * 32];                       // position the filter last resumed at
     int gap_done = (int) sb[F_GAPDONE * 32];                // outputs after it already corrected
     uint32_t sfrom = sb[F_SFROM * 32], sto = sb[F_STO * 32];    // span the search pass has covered
-    bool fixup = false, deferred = false;
+    bool fixup = false, deferred = false, yield = false;
+    // M17B_STREAMING, acquiring streams: at most kWalkBudget samples of block walk per round.  Waiting for the LSF sync
+    // word in a preamble the state machine correlates and updates its estimators on every symbol, an order of magnitude
+    // more serial work per sample than inside a frame; a round of the acquiring streams' chain (which has its own rounds,
+    // m17b_submit) lasts as long as its slowest walk, so a long one is taken in several rounds (the stream stays `lagging`).
+    // A stream that already trails the head by more than a submit walks on regardless (the sample ring is finite).
+    int budget = e.split && head - pos <= guard ? kWalkBudget : 0x7fffffff;
 
     Scan z;
     memset(&z, 0, sizeof(z));
@@ -1189,7 +1202,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     z.vcost = sb[F_VCOST * 32];
     z.sw = sb[F_SW * 32];
 
-    while (pos != head && !z.pending && !fixup && !deferred) {
+    while (pos != head && !z.pending && !fixup && !deferred && !yield) {
         if (!z.init && !z.dcd) {
             // ---- idle: M17Demodulator.h:675-689 ------------------------------------------------
             const uint32_t left = head - pos;
@@ -1274,6 +1287,9 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                 deferred = true;                            // this frame ends after the head: the next submit's
                 break;
             }
+            // M17B_STREAMING: an acquiring stream that has got as far as a frame is a receiving stream from here on:
+            // the receiving streams' chain takes it at its next round and walks the frame in step with the others
+            if (e.split) { yield = true; break; }
             // Aligned 8-sample blocks, every lane of the warp one block per pass, from here to the end of the
             // frame in ONE loop (the carrier-detect cadence, every 960 samples and always at a block end, is
             // handled inside it), so that the lanes of a warp, which all start their frames in the same pass of
@@ -1431,6 +1447,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
                 if (!z.dcd) { gate_off(d, e, z.gap_k, pos); break; }
             }
             if (pos == head || z.pending || z.state == ST_UNLOCKED) break;
+            if (!initializing && (budget -= j - jb) <= 0) { yield = true; break; }
             // inside a frame with nothing pending at index() == 0: the rest of the frame is the frame walk's
             if (!initializing && z.state == ST_FRAME && !z.need_reset && !z.need_update && z.gap_k >= kTapsUsed) break;
         }
@@ -1450,7 +1467,7 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
          ((uint32_t) z.ssi << FL_SSI_SHIFT) | ((uint32_t) z.csi << FL_CSI_SHIFT) |
          (z.dcd ? FL_DCD : 0) | (z.dcd_trig ? FL_DCD_TRIG : 0) | (z.need_reset ? FL_NEED_RESET : 0) |
          (z.need_update ? FL_NEED_UPDATE : 0) | (z.dev_reset ? FL_DEV_RESET : 0) | (z.eot ? FL_EOT : 0) |
-         (z.pending ? FL_PENDING : 0) | (fixup ? FL_FIXUP : 0);
+         (z.pending ? FL_PENDING : 0) | (fixup && e.cls != 0 ? FL_FIXUP : 0);
     sb[F_GAPR * 32] = gap_r;
     sb[F_GAPDONE * 32] = (uint32_t) gap_done;
     sb[F_SYNC_COUNT * 32] = (uint32_t) z.sync_count; sb[F_MISSING * 32] = (uint32_t) z.missing;
@@ -1463,7 +1480,9 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
     // whoever sees flags that make the stream its own must see the rest of the state as well.
     publish_fence();
     sb[F_FLAGS * 32] = fl;
-    if (fixup) d.fix_list[(size_t) e.cls * d.np + ctr_add(&d.ctr->cls[e.cls].fix_count, 1u)] = e.s;
+    // (a stream that stops for fixup_kernel is no longer `receiving`: if it was walked as one, the acquiring streams'
+    // chain picks it up as it stands, stops at once and files the request -- class 0 runs no fix-up kernels)
+    if (fixup && e.cls != 0) d.fix_list[(size_t) e.cls * d.np + ctr_add(&d.ctr->cls[e.cls].fix_count, 1u)] = e.s;
     if (z.pending) {
         // queue the frame by what M17FrameDecoder::operator() will do with it (M17FrameDecoder.h:353-392),
         // so that decode_kernel's warps each run one kind
@@ -1475,8 +1494,8 @@ M17B_FN void scan_lane(const DevPtrs& d, const LaneIo& e, uint32_t head, unsigne
         else if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) kind = 2;
         d.dec_list[(size_t) (e.cls * 5 + kind) * d.np + ctr_add(&d.ctr->cls[e.cls].dec_count[kind], 1u)] = e.s;
     }
-    if (deferred) ctr_add(&d.ctr->deferred, 1u);
-    else if (pos != head) ctr_add(&d.ctr->lagging, 1u);
+    if (deferred) ctr_add(&d.ctr->cls[e.cls].deferred, 1u);
+    else if (pos != head) ctr_add(&d.ctr->cls[e.cls].lagging, 1u);
 }
 
 // Fresh-demodulator state of one lane: the member initialisers of M17Demodulator
@@ -1495,10 +1514,11 @@ M17B_FN void init_lane(uint32_t* sb, uint32_t pos0 = 0)
     sb[F_POS * 32] = pos0; sb[F_GAPR * 32] = pos0; sb[F_SFROM * 32] = pos0; sb[F_STO * 32] = pos0;
 }
 
-M17B_FN LaneIo make_io(const DevPtrs& d, uint32_t s, const LlrTable* tab, int cls = 0)
+M17B_FN LaneIo make_io(const DevPtrs& d, uint32_t s, const LlrTable* tab, int cls = 0, bool split = false)
 {
     LaneIo e;
     e.cls = cls;
+    e.split = split;
     e.llr_tab = tab;
     e.sb = d.st + st_index(s, 0);
     e.sw_samples = d.sw_samples + s;
@@ -1556,7 +1576,7 @@ M17B_FN bool wants_search(const uint32_t* sb, uint32_t head)
 // End of the span a search request covers: the stream usually finds its sync word within a frame's worth of
 // samples, and what lies beyond would be searched for nothing (and keeps the whole round waiting: the limit
 // filter over the span is a serial recurrence).  A stream that is still searching at the end asks again.
-constexpr uint32_t kSearchSpan = 2048;
+constexpr uint32_t kSearchSpan = 4096;
 M17B_FN uint32_t search_end(uint32_t from, uint32_t head)
 {
     return head - from > kSearchSpan ? from + kSearchSpan : head;

@@ -69,8 +69,8 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.ckpt_ring.assign((size_t) d.ring_lines * np * 4, float2{0.f, 0.f});
     d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
     m.seg_ring.assign((size_t) d.n_seg * 4 * np, 0.f);
-    m.fix_list.assign(np, 0);
-    m.dec_list.assign(5 * np, 0);
+    m.fix_list.assign(2 * np, 0);
+    m.dec_list.assign(10 * np, 0);
     m.sw_samples.assign(30 * np, 0.f);
     m.fir_snap.assign((size_t) kTapsUsed * np, 0.f);
     m.llr.assign(184 * np, 0);
@@ -86,11 +86,11 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
 void round(Emu& m, bool defer)
 {
     DevPtrs& d = m.d;
-    m.ctr.lagging = 0;
-    m.ctr.deferred = 0;
-    m.ctr.cls[0].fix_count = 0;
-    for (int k = 0; k != 5; ++k) m.ctr.cls[0].dec_count[k] = 0;
-    for (uint32_t s = 0; s != d.n_streams; ++s) scan_lane(d, make_io(d, s, &m.tab), m.head, m.head64, true, defer);
+    m.ctr.cls[1].lagging = 0;
+    m.ctr.cls[1].deferred = 0;
+    m.ctr.cls[1].fix_count = 0;
+    for (int k = 0; k != 5; ++k) m.ctr.cls[1].dec_count[k] = 0;
+    for (uint32_t s = 0; s != d.n_streams; ++s) scan_lane(d, make_io(d, s, &m.tab, 1), m.head, m.head64, true, defer);
     if (const char* t = getenv("M17EMU_TRACE")) {
         const uint32_t s = (uint32_t) atoi(t);
         const uint32_t* sb = d.st + st_index(s, 0);
@@ -103,9 +103,9 @@ void round(Emu& m, bool defer)
     }
     uint16_t hist[244];
     for (int k = 0; k != 5; ++k)
-        for (uint32_t q = 0; q != m.ctr.cls[0].dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) k * d.np + q], hist, m.head, m.head64);
-    for (uint32_t q = 0; q != m.ctr.cls[0].fix_count; ++q) {
-        const uint32_t s = m.fix_list[q];
+        for (uint32_t q = 0; q != m.ctr.cls[1].dec_count[k]; ++q) decode_lane(d, m.dec_list[(size_t) (5 + k) * d.np + q], hist, m.head, m.head64);
+    for (uint32_t q = 0; q != m.ctr.cls[1].fix_count; ++q) {
+        const uint32_t s = m.fix_list[d.np + q];
         fixup_lane(d, s, m.head);
         search_lane(d, s, m.head);
         d.st[st_index(s, F_FLAGS)] &= ~FL_FIXUP;
@@ -178,12 +178,12 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
         // flags bit 1 = M17B_STREAMING: lanes may leave a partial frame for the next submit; only the
         // final flush (m17b_sync) brings every lane to the head
         for (int r = 0; r != rounds; ++r) round(m, streaming);
-        for (int extra = 0; m.ctr.lagging != 0; ++extra) {
+        for (int extra = 0; m.ctr.cls[1].lagging != 0; ++extra) {
             if (extra == 256) return -1;
             round(m, streaming);
         }
     }
-    for (int extra = 0; m.ctr.lagging != 0 || m.ctr.deferred != 0; ++extra) {
+    for (int extra = 0; m.ctr.cls[1].lagging != 0 || m.ctr.cls[1].deferred != 0; ++extra) {
         if (extra == 256) return -1;
         round(m, false);
     }
