@@ -34,14 +34,23 @@ sys.path.insert(0, ROOT)
 ALG_FLOP_PER_SAMPLE = 300.0          # 150 multiplies + 150 adds per filtered sample
 
 
+def kernel_source_hash():
+    """sha256 over the kernel sources: what a committed ncu capture is stamped with (the GPU box has no .git)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("m17b_kernels.cu", "m17b_lane.cuh", "m17b_dev.cuh"):
+        h.update(open(os.path.join(ROOT, "m17_cxx_demod_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def fir_traffic(channels, chunk, fma):
-    """DRAM bytes per fir_kernel launch from the committed ncu --set full capture (profiles/fir_dram_traffic.json),
-    or None when the capture was taken on another launch shape."""
+    """DRAM bytes per fir_kernel launch from the committed ncu --set full capture (profiles/fir_dram_traffic.json), or
+    None when that capture was taken on another launch shape or on other kernel sources than the ones that run here."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "fir_dram_traffic.json")))
     except OSError:
         return None
-    if fma or t["channels"] != channels or t["chunk_samples"] != chunk:
+    if fma or t["channels"] != channels or t["chunk_samples"] != chunk or t.get("kernel_source_hash") != kernel_source_hash():
         return None
     return t["dram_bytes_read"] + t["dram_bytes_write"]
 
@@ -221,7 +230,8 @@ def main():
     dev = torch.device("cuda", local)
 
     K, W, T = args.steps, args.warmup, args.chunk
-    total = (K + W) * T
+    P = 3                                                      # profiled steps after the timed ones (kernel shares)
+    total = (K + W + P) * T
     w, channels, desc = workload(args, total)
     U = len(w.params)
     lo, hi = shard_range(channels * world, world, rank)       # weak scaling: `channels` per GPU
@@ -237,7 +247,7 @@ def main():
     assert big.is_contiguous()
     torch.cuda.synchronize()
 
-    flags = m.PROFILE | m.STREAMING | (m.FIR_FMA if args.fma else 0)
+    flags = m.STREAMING | (m.FIR_FMA if args.fma else 0)      # per-kernel event records stay off in the timed steps
     rec_cap = min(channels * 2 * (T // 1600 + 2) * 3, 2**31 - 1)          # two steps in flight
     d = m.Demodulator(channels, T, flags=flags, device=local, frame_capacity=rec_cap)
     fp32_peak = d.measure_fp32_peak(1)
@@ -257,7 +267,6 @@ def main():
     for k in range(W):
         d.submit_device(big.data_ptr() + 2 * k * T, T, total)
         records.append(d.drain())
-    d.profile(reset=True)
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -288,6 +297,19 @@ def main():
     t_wall = time.perf_counter() - t_wall0
     t_dev = d.event_elapsed_ms(0, 1) * 1e-3      # CUDA events on the library's compute stream
     clocks = sampler.stop()
+    ctr_timed = d.counters()
+    # Kernel shares: P more steps of the same stream of samples, enqueued the same way, with the per-kernel event
+    # records on (two event records around every launch: kept out of the timed steps).
+    d.profile_enable(True)
+    d.profile(reset=True)
+    prev = None
+    for k in range(W + K, W + K + P):
+        d.submit_device(big.data_ptr() + 2 * k * T, T, total)
+        t_k = d.ticket()
+        if prev is not None:
+            records.append(d.drain_upto(prev))
+        prev = t_k
+    records.append(d.drain())
     prof = d.profile()
     ctr = d.counters()
     # Timed on the device (events on the launching stream); the host clock around the same K steps
@@ -303,6 +325,7 @@ def main():
     # of step k+1, so the filter's in-step launch time includes that time-sharing.  Three more submits, each
     # followed by m17b_sync, time the same launch (same shapes, same resident data) with nothing else running.
     fir_in_step_ms = prof.fir_ms / max(1, prof.fir_launches)
+    fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     d.profile(reset=True)
     for k in range(3):
         d.submit_device(big.data_ptr() + 2 * k * T, T, total)
@@ -310,13 +333,35 @@ def main():
     d.drain()
     prof_alone = d.profile()
     fir_ms_per_launch = prof_alone.fir_ms / max(1, prof_alone.fir_launches)
-    fir_samples_per_launch = prof.fir_samples / max(1, prof.fir_launches)
     achieved = ALG_FLOP_PER_SAMPLE * fir_samples_per_launch / (fir_ms_per_launch * 1e-3) / 1e12 if fir_ms_per_launch else 0.0
     kernel_ms = {"fir": prof.fir_ms, "dcd": prof.dcd_ms, "scan": prof.scan_ms, "scan_acquiring": prof.scan1_ms, "decode": prof.decode_ms, "fixup_search": prof.fixup_ms,
                  "tail": prof.aux_ms}
     ksum = sum(kernel_ms.values()) or 1.0
-    launches = int(prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches +
-                   prof.fixup_launches)
+    launches_per_step = (prof.fir_launches + prof.dcd_launches + prof.aux_launches + prof.scan_launches + prof.decode_launches +
+                         prof.fixup_launches) / P
+    launches = int(round(launches_per_step * K))
+    # achieved HBM figures of the latency-bound kernels (north_star asks for them): algorithmic bytes per step over the
+    # kernels' summed launch time (events of the profiled steps; launches of different chains overlap, so these are lower bounds)
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+        hbm_src = "MEASURED_PEAKS.json hbm_gbs"
+    except (OSError, KeyError, ValueError):
+        hbm_peak, hbm_src = 6550.0, "fallback stated in B200_PROFILING.md"
+    frames_step = n_frames / K
+    samples_step = channels * T
+
+    def hbm_entry(alg_bytes, ms, n_launch, what):
+        gbs = alg_bytes / (ms * 1e-3) / 1e9 if ms else None
+        return {"algorithmic_bytes_per_step": alg_bytes, "what": what, "kernel_ms_per_step": ms, "launches_per_step": n_launch,
+                "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_peak if gbs else None, "bound": "latency (dependent issue), not HBM"}
+    roofline_hbm = {
+        "peak_gbs": hbm_peak, "peak_source": hbm_src,
+        "dcd": hbm_entry(4.0 * samples_step, prof.dcd_ms / P, prof.dcd_launches / P, "4 B/sample read (x[n] - x[n-120])"),
+        "scan": hbm_entry(4.0 * samples_step + 368.0 * frames_step, (prof.scan_ms + prof.scan1_ms) / P, prof.scan_launches / P,
+                          "4 B/sample read (matched-filter output) + 368 B/frame written (soft bits)"),
+        "decode": hbm_entry((368.0 + 80.0) * frames_step, prof.decode_ms / P, prof.decode_launches / P,
+                            "368 B/frame read (soft bits) + 80 B/record written"),
+    }
 
     line = {
         "metric": "baseband_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -344,23 +389,26 @@ def main():
                          "fmul_fadd_tflops": mix_scalar, "fmul_fadd2_tflops": mix_packed,
                          "frac_of_ceiling": achieved / max(mix_scalar, mix_packed) if max(mix_scalar, mix_packed) > 0 else None}},
         "kernel_share": {k: v / ksum for k, v in kernel_ms.items()},
-        "kernel_ms_per_step": {k: v / K for k, v in kernel_ms.items()},
+        "kernel_ms_per_step": {k: v / P for k, v in kernel_ms.items()},
+        "kernel_timing": f"CUDA events around every launch during {P} further steps after the timed ones (none inside the timed steps); launches of the two chains and of the next step's front end overlap, so the sum exceeds the step",
+        "roofline_hbm": roofline_hbm,
         "gpu_launches": launches,
-        "search": {"requests_per_step": prof.search_requests / K, "samples_per_step": prof.search_samples / K,
+        "search": {"requests_per_step": prof.search_requests / P, "samples_per_step": prof.search_samples / P,
                    "note": "streams in ST_UNLOCKED with the carrier detect on ask for a parallel sync-word search over the samples ahead"},
         "clocks": clocks,
-        "frames_by_type": list(ctr.frames), "faults": int(ctr.faults), "dropped": int(ctr.dropped),
+        "frames_by_type": list(ctr_timed.frames), "faults": int(ctr.faults), "dropped": int(ctr.dropped),
     }
 
     # ---- parity of the benchmarked run itself: every channel against the oracle of its waveform ----
     if rank == 0 and not args.no_parity:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_lib as ol
-        n_chk = min(U, 64)
+        n_chk = U                                              # every waveform, hence every channel
         want, _ = ol.demod_batch("ref" if ol.have_ref() else "port", uniq[:n_chk, :])
         allrec = np.concatenate(records) if records else np.zeros(0, m.FRAME_DTYPE)
         per = m.demod.split_by_stream(allrec, channels)
         bad = 0
+        bad_rec = 0
         checked = 0
         examples = []
         for s in range(channels):
@@ -370,9 +418,19 @@ def main():
             checked += 1
             if not ol.records_equal(want[u], per[s]):
                 bad += 1
+                a, b = want[u], per[s]
+                n = min(len(a), len(b))
+                same = np.ones(n, bool)
+                for f in ("seq", "viterbi_cost", "type", "payload", "lsf", "sample_pos"):
+                    same &= (a[f][:n] == b[f][:n]) if a[f].ndim == 1 else (a[f][:n] == b[f][:n]).all(axis=1)
+                bad_rec += int((~same).sum()) + abs(len(a) - len(b))
                 if len(examples) < 4:
                     examples.append(f"channel {s} (waveform {u}): " + ol.describe_mismatch(want[u], per[s]))
-        line["parity"] = {"channels_checked": checked, "mismatching": bad, "oracle": "ref" if ol.have_ref() else "port"}
+        total_rec = int(sum(len(per[s]) for s in range(channels)))
+        line["parity"] = {"channels": channels, "channels_checked": checked, "mismatching": bad, "records_compared": total_rec,
+                          "mismatching_records": bad_rec,
+                          "oracle": "ref" if ol.have_ref() else "port",
+                          "what": f"all records of all {K + W + P} steps, every channel against the oracle's records of its waveform, all fields bit for bit"}
         if examples:
             line["parity"]["examples"] = examples
 
@@ -390,7 +448,7 @@ def main():
         if (Ke + NW) * T > total:
             Ke = total // T - NW
         DEPTH = 2                                              # submits enqueued ahead of the record read-back
-        de = m.Demodulator(channels, T, flags=m.PROFILE | m.STREAMING, device=local,
+        de = m.Demodulator(channels, T, flags=m.STREAMING, device=local,
                            frame_capacity=min(channels * (DEPTH + 2) * (T // 1600 + 2) * 3, 2**31 - 1))
         bufs = [m.demod.PinnedBuffer((channels, T)) for _ in range(Ke + NW)]
         idx_h = (np.arange(lo, hi) % U)
@@ -399,7 +457,6 @@ def main():
         for k in range(NW):
             de.submit(bufs[k].array)
             de.drain()
-        de.profile(reset=True)
         barrier()
         t0 = time.perf_counter()
         marks = []
@@ -426,7 +483,14 @@ def main():
             fr += len(r)
         barrier()
         te = time.perf_counter() - t0
+        # upload rate and kernel times of this mode from two more submits with the event records on (outside the timing)
+        de.profile_enable(True)
+        de.profile(reset=True)
+        for k in range(2):
+            de.submit(bufs[k].array)
+        de.drain()
         prof_e = de.profile()
+        Kp = 2
         tt = torch.tensor([te], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -435,8 +499,8 @@ def main():
                        "h2d_bytes_per_step": channels * T * 2, "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
                        "frames_per_s": world * fr / te, "pipeline_depth": DEPTH,
                        "ms_between_drains": [round(1e3 * (b - a), 2) for a, b in zip([t0] + marks[:-1], marks)],
-                       "kernel_ms_per_step": {"fir": prof_e.fir_ms / Ke, "dcd": prof_e.dcd_ms / Ke, "scan": prof_e.scan_ms / Ke,
-                                              "decode": prof_e.decode_ms / Ke, "h2d": prof_e.h2d_ms / Ke},
+                       "kernel_ms_per_step": {"fir": prof_e.fir_ms / Kp, "dcd": prof_e.dcd_ms / Kp, "scan": prof_e.scan_ms / Kp,
+                                              "scan_acquiring": prof_e.scan1_ms / Kp, "decode": prof_e.decode_ms / Kp, "h2d": prof_e.h2d_ms / Kp},
                        "h2d_gbs": (prof_e.h2d_bytes / (prof_e.h2d_ms * 1e-3) / 1e9) if prof_e.h2d_ms else None,
                        "timing": "host clock around Ke submit+drain pairs incl. pipeline fill and final drain"}
         for b in bufs:

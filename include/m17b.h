@@ -211,6 +211,9 @@ int  m17b_diag_get(m17b_ctx* ctx, uint32_t stream, m17b_diag* out);
 int  m17b_diag_drain(m17b_ctx* ctx, m17b_diag_rec* out, size_t cap, size_t* n);
 int  m17b_counters_get(m17b_ctx* ctx, m17b_counters* out);
 int  m17b_get_profile(m17b_ctx* ctx, m17b_profile* out, int reset);
+/* Switch the per-kernel event records of M17B_PROFILE on or off for the submits that follow (m17b_sync first), so that a
+ * benchmark can time its steps without them and take the kernel shares from a separate pass. */
+int  m17b_profile_enable(m17b_ctx* ctx, int on);
 
 /* Device-side timing for benchmarks: record CUDA event `slot` (0..7) on the context's compute
  * stream now; elapsed milliseconds between two recorded slots (synchronises on `b`). */

@@ -692,6 +692,15 @@ int m17b_get_profile(m17b_ctx* c, m17b_profile* out, int reset)
     return M17B_OK;
 }
 
+int m17b_profile_enable(m17b_ctx* c, int on)
+{
+    if (!c) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    c->profile = on != 0;
+    return M17B_OK;
+}
+
 int m17b_event_record(m17b_ctx* c, int slot)
 {
     if (!c || slot < 0 || slot >= 8) return M17B_EINVAL;

@@ -83,7 +83,7 @@ def load_library() -> ctypes.CDLL:
                      "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_debug_correlate", "m17b_diag_drain",
                      "m17b_measure_fp32_peak",
                      "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count",
-                     "m17b_event_record", "m17b_event_elapsed"):
+                     "m17b_event_record", "m17b_event_elapsed", "m17b_profile_enable"):
             getattr(lib, name).restype = ctypes.c_int
         lib.m17b_submit.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int]
         lib.m17b_sync.argtypes = [ctypes.c_void_p]
@@ -111,6 +111,7 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_debug_correlate.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
                                              ctypes.c_void_p, ctypes.c_void_p]
         lib.m17b_diag_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
+        lib.m17b_profile_enable.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.m17b_event_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.m17b_event_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
         lib.m17b_measure_fp32_peak.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
@@ -266,6 +267,9 @@ class Demodulator:
         p = Profile()
         self._check(self._lib.m17b_get_profile(self._ctx, ctypes.byref(p), int(reset)), "m17b_get_profile")
         return p
+
+    def profile_enable(self, on: bool):
+        self._check(self._lib.m17b_profile_enable(self._ctx, int(on)), "m17b_profile_enable")
 
     def debug_filter(self, samples: np.ndarray):
         """Matched filter only: returns (filtered, scaled) float32 [n_streams, n]."""

@@ -2,6 +2,7 @@
 seeded inputs.  Integer/byte results (frame records) bit-exact; matched-filter outputs bit-exact in
 the default mode and within 1e-5 relative in FMA mode (the tolerance BASELINE.json states)."""
 import ctypes
+import json
 import os
 import subprocess
 
@@ -181,14 +182,18 @@ def test_many_channels_tiled_property():
 
 
 def test_fma_filter_mode_payloads():
-    """FMA mode is not bit-identical in the filter; report how the decoded records compare."""
+    """FMA mode is not bit-identical in the filter, so it is not the product mode: the decoded records differ for a
+    few streams (a soft decision or a sync-word trigger that lies within the filter's 1e-5).  The count observed on
+    this corpus is pinned, so that a change of it is noticed; exact mode must give 0 (all other tests)."""
     x = gen.generate(random_params(9, gen.STREAM, 64), 96000)
     want, _ = ol.demod_batch("port", x)
     with m.Demodulator(64, 24000, flags=m.FIR_FMA) as d:
         got = d.demodulate(x, chunk=24000)
     same = sum(ol.records_equal(a, b) for a, b in zip(want, got))
-    print(f"FMA filter: {same}/64 streams still bit-identical in all records")
-    assert same >= 48
+    n_rec = sum(len(r) for r in want)
+    print(f"FMA filter: {same}/64 streams bit-identical in all {n_rec} records")
+    expect = json.load(open(os.path.join(HERE, "golden", "fma_mode_expect.json")))
+    assert {"streams_identical": same, "streams": 64, "records": n_rec} == expect
 
 
 def test_cli_frames_mode_matches_oracle(tmp_path):
