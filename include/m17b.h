@@ -142,7 +142,37 @@ typedef struct m17b_counters {
     uint64_t golay_fail;       /* LICH frames with an uncorrectable Golay word (:195)      */
     uint64_t faults;           /* internal invariant violations (must stay 0)              */
     uint64_t dropped;          /* frame records lost to ring overflow (must stay 0)        */
+    /* consumers of the frame records, per stream on the device (apps/m17-demod.cpp:207-253,287-305): */
+    uint64_t packets_ok;       /* packets reassembled whose CRC-16/X.25 residue is 0x0f47  */
+    uint64_t packets_crc_fail; /* last segment seen, checksum wrong                        */
+    uint64_t packet_seq_errors;/* segments dropped: frame number out of sequence           */
+    uint64_t packets_dropped;  /* packet records lost to ring overflow (must stay 0)       */
 } m17b_counters;
+
+/* What the reference CLI keeps per process on top of the frame callbacks, kept here per stream on the device
+ * (decode_kernel feeds it): packet reassembly with sequence and CRC check (apps/m17-demod.cpp:80-175,207-253:
+ * an LSF record clears the buffer -- and seeds it with the LSF for packet-mode types other than 1 --, every
+ * non-final segment whose frame number is the expected one appends 25 bytes, the final segment appends its byte
+ * count and the CRC-16/X.25 residue is checked; like the reference the buffer is not cleared by a final segment)
+ * and PRBS9 bit-error accounting over BERT frames (decode_bert :287-305, Util.h:320-413, reset by the diagnostic
+ * callback when it reports no carrier, :353-355). */
+#define M17B_PACKET_MAX 860    /* 30 (LSF) + 33 segments of 25 bytes; a buffer that would grow past this stops growing */
+typedef struct m17b_packet {
+    uint32_t stream;
+    uint32_t seq;              /* ordinal of this record within its stream                 */
+    uint64_t sample_pos;       /* input sample that completed the final segment            */
+    uint16_t length;           /* bytes in data[] (buffer contents incl. the 2 FCS bytes)  */
+    uint8_t  fcs_ok;           /* CRC-16/X.25 residue == 0x0f47                            */
+    uint8_t  pad;
+    uint8_t  data[M17B_PACKET_MAX];
+} m17b_packet;                 /* 880 bytes */
+
+typedef struct m17b_ber {
+    int32_t  synced;           /* PRBS9::synced                                            */
+    uint32_t bits;             /* PRBS9::bit_count                                         */
+    uint32_t errors;           /* PRBS9::err_count                                         */
+    uint32_t packet_bytes;     /* bytes currently in the stream's packet buffer            */
+} m17b_ber;
 
 /* Accumulated device time per kernel (CUDA events on the launching stream),
  * only when M17B_PROFILE is set. */
@@ -210,6 +240,11 @@ int  m17b_diag_get(m17b_ctx* ctx, uint32_t stream, m17b_diag* out);
  * chronological order; call again while *n == cap. */
 int  m17b_diag_drain(m17b_ctx* ctx, m17b_diag_rec* out, size_t cap, size_t* n);
 int  m17b_counters_get(m17b_ctx* ctx, m17b_counters* out);
+/* m17b_sync(), then move up to `cap` packet records (one per final packet segment a stream decoded, checksum right or
+ * wrong) to `out`, per stream in chronological order; call again while *n == cap. */
+int  m17b_packet_drain(m17b_ctx* ctx, m17b_packet* out, size_t cap, size_t* n);
+/* The stream's PRBS9 accounting (what the reference prints as "BER: errors / bits") after m17b_sync(). */
+int  m17b_ber_get(m17b_ctx* ctx, uint32_t stream, m17b_ber* out);
 int  m17b_get_profile(m17b_ctx* ctx, m17b_profile* out, int reset);
 /* Switch the per-kernel event records of M17B_PROFILE on or off for the submits that follow (m17b_sync first), so that a
  * benchmark can time its steps without them and take the kernel shares from a separate pass. */

@@ -9,6 +9,7 @@
 // mode; with --frames one text record per frame callback in the format of
 // oracle/_ref/m17-demod-ref, which is what the parity tests diff.
 #include "m17cxx_b200/M17Demodulator.h"
+#include "m17cxx_b200/ax25_frame.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -110,7 +111,11 @@ bool decode_packet(const std::array<uint8_t, 26>& seg)
         uint16_t checksum = crc_x25(current_packet.data(), current_packet.size());
         // boost::crc_optimal<16,0x1021,0xFFFF,0xFFFF,true,true> over data+FCS leaves 0x0f47
         if (checksum == 0x0f47) {
-            std::cerr << "\nPacket: " << std::dec << current_packet.size() << " bytes, FCS ok" << std::endl;
+            // the reference prints the packet as an AX.25 frame on stderr (:224-229); the packet itself also goes to
+            // stdout here (this CLI's stdout carries the decoded payloads)
+            mobilinkd::ax25_frame frame(std::string(current_packet.begin(), current_packet.end()));
+            std::cerr << '\n';
+            mobilinkd::write(std::cerr, frame);
             std::cout.write(reinterpret_cast<const char*>(current_packet.data()), std::streamsize(current_packet.size()));
             return true;
         }
@@ -180,8 +185,9 @@ void diagnostic_callback(bool dcd, float evm, float deviation, float offset, boo
                   << "ppm, sample: " << std::setw(1) << sample_index << ", " << sync_index << ", " << clock_index
                   << ", cost: " << std::setfill(' ') << std::setw(3) << viterbi_cost;
     }
-    if (!dcd && prbs.synced && prbs.bit_count > 0) prbs.reset();
-    if (prbs.synced && prbs.bit_count > 0 && !quiet) {
+    // (prbs.bits() of the reference asserts `synced`; built with NDEBUG, as its CMake release build is, it is bit_count)
+    if (!dcd && prbs.bit_count > 0) prbs.reset();
+    if (prbs.bit_count > 0 && !quiet) {
         std::cerr << (debug ? ", " : "\r");
         char buffer[40];
         std::snprintf(buffer, 40, "BER: %-1.6lf (%lu bits)", double(prbs.err_count) / double(prbs.bit_count), (unsigned long) prbs.bit_count);
@@ -224,6 +230,17 @@ int main(int argc, char* argv[])
         else if (a == "-q" || a == "--quiet") quiet = true;
         else if (a == "--frames") frames_mode = true;
         else if (a == "--fma") fma = true;
+        else if (a == "--ax25-print" && i + 1 < argc) {
+            // test hook: print the file's bytes the way a reassembled packet is printed (no device needed)
+            std::FILE* f = std::fopen(argv[++i], "rb");
+            if (!f) return EXIT_FAILURE;
+            std::string bytes;
+            int ch;
+            while ((ch = std::fgetc(f)) != EOF) bytes.push_back(char(ch));
+            std::fclose(f);
+            mobilinkd::write(std::cout, mobilinkd::ax25_frame(bytes));
+            return EXIT_SUCCESS;
+        }
         else { std::cerr << "unrecognised option '" << a << "'" << std::endl; usage(); return 0; }
     }
     if (int(debug) + int(verbose) + int(quiet) > 1) {

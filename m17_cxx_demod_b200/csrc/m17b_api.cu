@@ -69,6 +69,7 @@ struct m17b_ctx {
     uint32_t rec_read = 0;                     // record cursor consumed by the host (monotonic, mod 2^32)
     unsigned long long dropped_reported = 0;   // overflow already signalled to the caller (M17B_EOVERFLOW is returned once per loss)
     uint32_t diag_read = 0;                    // diagnostic-record cursor consumed by the host
+    uint32_t pkt_read = 0;                     // packet-record cursor consumed by the host
 };
 
 namespace {
@@ -229,7 +230,7 @@ void free_all(m17b_ctx* c)
     cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.mask_ring); cudaFree(c->d.ckpt_ring);
     cudaFree(c->d.corr_snap); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.scan_list); cudaFree(c->d.dec_list); cudaFree(c->d.diag_recs);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
-    cudaFree(c->d.recs); cudaFree(c->d.ctr);
+    cudaFree(c->d.recs); cudaFree(c->d.ctr); cudaFree(c->d.pkt_buf); cudaFree(c->d.pkt_recs);
     if (c->ready) cudaFreeHost(c->ready);
     for (int i = 0; i != 2; ++i) {
         cudaFree(c->tail[i]); cudaFree(c->stage[i]);
@@ -346,6 +347,9 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
             d.diag_cap = next_pow2((uint32_t) std::min<uint64_t>((uint64_t) cfg->n_streams * 3 * (cfg->max_chunk / 384 + 2), 0x40000000ull));
             CK(cudaMalloc(&d.diag_recs, (size_t) d.diag_cap * sizeof(m17b_diag_rec)));
         }
+        d.pkt_cap = next_pow2(std::max(64u, cfg->n_streams));
+        CK(cudaMalloc(&d.pkt_buf, np * (size_t) kPktStride));
+        CK(cudaMalloc(&d.pkt_recs, (size_t) d.pkt_cap * sizeof(m17b_packet)));
         // a scan lane may lag the head by the ring span; its window starts up to 960 samples earlier, and the
         // first window's entry must survive 1920 samples longer
         d.n_seg = next_pow2((d.ring_lines * (uint32_t) kLine + 1920u) / (uint32_t) kSeg + 2u);
@@ -673,6 +677,44 @@ int m17b_counters_get(m17b_ctx* c, m17b_counters* out)
     out->golay_fail = c->host_ctr.golay_fail;
     out->faults = c->host_ctr.faults;
     out->dropped = c->host_ctr.dropped;
+    out->packets_ok = c->host_ctr.packets_ok;
+    out->packets_crc_fail = c->host_ctr.packets_crc_fail;
+    out->packet_seq_errors = c->host_ctr.packet_seq_errors;
+    out->packets_dropped = c->host_ctr.packets_dropped;
+    return M17B_OK;
+}
+
+int m17b_packet_drain(m17b_ctx* c, m17b_packet* out, size_t cap, size_t* n)
+{
+    if (!c || !n || (!out && cap)) return M17B_EINVAL;
+    *n = 0;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    uint32_t avail = c->host_ctr.pkt_count - c->pkt_read;
+    if (avail > c->d.pkt_cap) { c->pkt_read = c->host_ctr.pkt_count - c->d.pkt_cap; avail = c->d.pkt_cap; }
+    const uint32_t k = (uint32_t) std::min<size_t>(cap, avail);
+    const uint32_t first = c->pkt_read & (c->d.pkt_cap - 1);
+    const uint32_t n1 = std::min(k, c->d.pkt_cap - first);
+    if (n1) CK(cudaMemcpy(out, c->d.pkt_recs + first, sizeof(m17b_packet) * n1, cudaMemcpyDeviceToHost));
+    if (k != n1) CK(cudaMemcpy(out + n1, c->d.pkt_recs, sizeof(m17b_packet) * (k - n1), cudaMemcpyDeviceToHost));
+    c->pkt_read += k;
+    c->d.pkt_read = c->pkt_read;
+    *n = k;
+    return M17B_OK;
+}
+
+int m17b_ber_get(m17b_ctx* c, uint32_t stream, m17b_ber* out)
+{
+    if (!c || !out || stream >= c->cfg.n_streams) return M17B_EINVAL;
+    int rc = m17b_sync(c);
+    if (rc != M17B_OK && rc != M17B_EOVERFLOW) return rc;
+    uint32_t f[NFIELDS];
+    CK(cudaMemcpy2D(f, sizeof(uint32_t), c->d.st + st_index(stream, 0), 32 * sizeof(uint32_t), sizeof(uint32_t),
+                    NFIELDS, cudaMemcpyDeviceToHost));
+    out->synced = (int32_t) ((f[F_PRBS] >> 9) & 1u);
+    out->bits = f[F_BER_BITS];
+    out->errors = f[F_BER_ERRS];
+    out->packet_bytes = f[F_PKT] & 0xFFFFu;
     return M17B_OK;
 }
 

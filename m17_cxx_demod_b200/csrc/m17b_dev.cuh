@@ -49,6 +49,7 @@ constexpr int kDftN = 120;            // NSlidingDFT length (M17Demodulator.h:14
 constexpr int kRoundCap = 2048;       // ring slack: samples a stream may trail the head by beyond one submit
 constexpr int kMinFrameSpacing = 1600;// lower bound on samples between two frame completions
 constexpr int kSeg = 192;             // gcd of the carrier-detect cadences 384 / 960 and of the 1920-sample start-up
+constexpr int kPktStride = 864;       // bytes of packet buffer per stream (>= M17B_PACKET_MAX, multiple of 16)
 constexpr int kClasses = 2;           // walk classes a round sorts the streams into (classify_kernel)
 constexpr int kFirstUpdate = 1920 + 384;   // position of a stream's first carrier-detect update (M17Demodulator.h:659-689)
 
@@ -73,7 +74,12 @@ enum Field : int {
     F_GAPDONE,      // outputs after F_GAPR already corrected by fixup_kernel (0..149)
     F_ACC1,         // dcd_kernel: five rolling carrier-detect energy sums of bin 0 (window phases), F_ACC1 + i
     F_ACC2 = F_ACC1 + 5,   // ... of bin 1
-    NFIELDS = F_ACC2 + 5
+    // consumers of the frame records (apps/m17-demod.cpp's per-process state, per stream here)
+    F_PKT = F_ACC2 + 5,    // packet buffer length (16) | packet_frame_counter (8) << 16 | packet ordinal (8) << 24
+    F_PRBS,         // PRBS9: state (9) | synced << 9 | sync_count (5) << 10 | hist_count (8) << 15 | hist_pos (7) << 23 | reset after the pending frame << 30
+    F_BER_BITS, F_BER_ERRS,
+    F_BER_H0,       // PRBS9::history, 128 bits, F_BER_H0 + i
+    NFIELDS = F_BER_H0 + 4
 };
 
 // F_FLAGS bit layout
@@ -116,6 +122,9 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
     unsigned long long diag_dropped;
     unsigned long long search_requests;   // sync-word searches served by search_mask_kernel
     unsigned long long search_samples;    // ... and the samples they covered
+    unsigned long long packets_ok, packets_crc_fail, packet_seq_errors, packets_dropped;
+    unsigned int pkt_count;       // packet-record cursor, monotonic like rec_count
+    unsigned int pad1;
 };
 
 struct DevPtrs {
@@ -138,6 +147,8 @@ struct DevPtrs {
     uint8_t* dec_bytes;           // [56][Np]
     m17b_frame* recs;             // [rec_cap]
     m17b_diag_rec* diag_recs;     // [diag_cap] or null: diagnostics at the reference's update points (M17B_DIAG_RECORDS)
+    uint8_t* pkt_buf;             // [Np][kPktStride] packet reassembly buffer of every stream (current_packet)
+    m17b_packet* pkt_recs;        // [pkt_cap]
     Counters* ctr;
     uint32_t n_streams;
     uint32_t np;                  // padded stream count (multiple of 128)
@@ -147,6 +158,8 @@ struct DevPtrs {
     uint32_t rec_read;            // cursor up to which the host has taken the records (at launch time)
     uint32_t diag_cap;            // power of two
     uint32_t diag_read;
+    uint32_t pkt_cap;             // power of two
+    uint32_t pkt_read;
 };
 
 __host__ __device__ inline size_t st_index(uint32_t s, int f)

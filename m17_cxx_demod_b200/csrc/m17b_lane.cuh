@@ -1104,8 +1104,26 @@ M17B_FN_COLD void emit_diag_rec(const DevPtrs& d, uint32_t s, const m17b_diag& v
     r->d = v;
 }
 
+M17B_FN void prbs_reset(uint32_t* sb)                                 // PRBS9::reset, Util.h:401-411
+{
+    sb[F_PRBS * 32] = 1u;
+    sb[F_BER_BITS * 32] = 0; sb[F_BER_ERRS * 32] = 0;
+    for (int i = 0; i != 4; ++i) sb[(F_BER_H0 + i) * 32] = 0;
+}
+
+// What apps/m17-demod.cpp's diagnostic callback does besides printing (:353-355): a callback that reports no
+// carrier resets the PRBS9 accounting once it has counted anything.  (The callback of a sample runs after that
+// sample's frame callback: when the frame it completes is still waiting for decode_kernel, the reset waits too.)
+M17B_FN void ber_diag_hook(uint32_t* sb, const Scan& z)
+{
+    if (z.dcd || sb[F_BER_BITS * 32] == 0) return;
+    if (z.pending) sb[F_PRBS * 32] |= 1u << 30;
+    else prbs_reset(sb);
+}
+
 M17B_FN void emit_diag(const DevPtrs& d, const LaneIo& e, const Scan& z, unsigned long long samples, bool locked_path)
 {
+    ber_diag_hook(e.sb, z);
     if (!d.diag_recs) return;
     m17b_diag v;
     v.dcd = z.dcd ? 1 : 0;
@@ -1510,6 +1528,7 @@ M17B_FN void init_lane(uint32_t* sb, uint32_t pos0 = 0)
     sb[F_IDX * 32] = (uint32_t) kTapsUsed << 24;             // no filter gap pending
     sb[F_FLAGS * 32] = FL_DEV_RESET | ((uint32_t) ST_UNLOCKED << FL_STATE_SHIFT) | ((uint32_t) SW_LSF << FL_SWT_SHIFT);
     sb[F_DEC * 32] = DEC_LSF;
+    sb[F_PRBS * 32] = 1u;                                    // PRBS9::state{1}
     // ring position of the stream's first sample (0 but for the wrap-around test hook)
     sb[F_POS * 32] = pos0; sb[F_GAPR * 32] = pos0; sb[F_SFROM * 32] = pos0; sb[F_STO * 32] = pos0;
 }
@@ -1882,6 +1901,108 @@ M17B_FN_COLD bool unpack_lich(const int16_t* llr, size_t np, uint8_t* lich)
     return true;
 }
 
+// ---------------------------------------------------------------------------
+// Consumers of the frame records: what apps/m17-demod.cpp keeps per process on top of the decoder's
+// callbacks, kept per stream here and fed by decode_lane.
+// ---------------------------------------------------------------------------
+
+// dump_lsf's bookkeeping (apps/m17-demod.cpp:154-175): a new LSF clears the packet buffer and the frame
+// counter; for a packet-mode LSF (type bit 0 clear) of a packet type other than 1 the buffer starts with the LSF.
+// (The reference indexes lsf[109..111] of the 30-byte array there; the intended test is the TYPE field's bits.)
+M17B_FN_COLD void consume_lsf(const DevPtrs& d, uint32_t s, uint32_t* sb, const uint8_t* lsf /* column, stride np */, size_t np)
+{
+    uint8_t* buf = d.pkt_buf + (size_t) s * kPktStride;
+    uint32_t len = 0;
+    const uint32_t b13 = lsf[(size_t) 13 * np];
+    if (!(b13 & 1u) && ((b13 >> 1) & 3u) != 1u) {
+        for (int i = 0; i != 30; ++i) buf[i] = lsf[(size_t) i * np];
+        len = 30;
+    }
+    sb[F_PKT * 32] = len | (sb[F_PKT * 32] & 0xFF000000u);           // packet_frame_counter = 0
+}
+
+// decode_packet (apps/m17-demod.cpp:207-253): reassembly, sequence check, CRC-16/X.25
+// (boost::crc_optimal<16, 0x1021, 0xFFFF, 0xFFFF, true, true>, residue 0x0f47 over data + FCS).
+M17B_FN_COLD void consume_packet(const DevPtrs& d, uint32_t s, uint32_t* sb, const uint8_t* seg /* 26 bytes */,
+                                 unsigned long long sample_pos)
+{
+    uint8_t* buf = d.pkt_buf + (size_t) s * kPktStride;
+    const uint32_t pk = sb[F_PKT * 32];
+    uint32_t len = pk & 0xFFFFu, counter = (pk >> 16) & 0xFFu, ordinal = pk >> 24;
+    const uint32_t number = (seg[25] & 0x7Fu) >> 2;
+    if (seg[25] & 0x80u) {                                            // last frame of the packet
+        const uint32_t n = number < 25u ? number : 25u;
+        for (uint32_t i = 0; i != n && len < (uint32_t) M17B_PACKET_MAX; ++i) buf[len++] = seg[i];
+        uint32_t reg = 0xFFFFu;
+        for (uint32_t i = 0; i != len; ++i) {
+            reg ^= buf[i];
+            for (int b = 0; b != 8; ++b) reg = (reg & 1u) ? (reg >> 1) ^ 0x8408u : reg >> 1;
+        }
+        const bool ok = ((~reg) & 0xFFFFu) == 0x0f47u;
+        ctr_add(ok ? &d.ctr->packets_ok : &d.ctr->packets_crc_fail, 1ull);
+        const uint32_t slot = ctr_add(&d.ctr->pkt_count, 1u);
+        if (slot - d.pkt_read >= d.pkt_cap) ctr_add(&d.ctr->packets_dropped, 1ull);
+        else {
+            m17b_packet* r = d.pkt_recs + (slot & (d.pkt_cap - 1));
+            r->stream = s; r->seq = ordinal; r->sample_pos = sample_pos;
+            r->length = (uint16_t) len; r->fcs_ok = ok ? 1 : 0; r->pad = 0;
+            for (uint32_t i = 0; i != len; ++i) r->data[i] = buf[i];
+        }
+        ordinal = (ordinal + 1u) & 0xFFu;
+    } else if (number != counter) {
+        ctr_add(&d.ctr->packet_seq_errors, 1ull);                     // segment dropped, counter unchanged
+    } else {
+        counter = (counter + 1u) & 0xFFu;
+        for (uint32_t i = 0; i != 25u && len < (uint32_t) M17B_PACKET_MAX; ++i) buf[len++] = seg[i];
+    }
+    sb[F_PKT * 32] = len | (counter << 16) | (ordinal << 24);
+}
+
+// PRBS9 (Util.h:320-413) in the per-stream fields; history = 128 bits in F_BER_H0 .. +3
+struct Prbs9 {
+    uint32_t state, synced, sync_count, hist_count, hist_pos, bits, errs, h[4];
+};
+
+// decode_bert (apps/m17-demod.cpp:287-305): 24 bytes + 5 bits through PRBS9::validate
+M17B_FN_COLD void consume_bert(uint32_t* sb, const uint8_t* bert /* 25 bytes */)
+{
+    const uint32_t w = sb[F_PRBS * 32];
+    Prbs9 p;
+    p.state = w & 0x1FFu; p.synced = (w >> 9) & 1u; p.sync_count = (w >> 10) & 31u;
+    p.hist_count = (w >> 15) & 0xFFu; p.hist_pos = (w >> 23) & 0x7Fu;
+    p.bits = sb[F_BER_BITS * 32]; p.errs = sb[F_BER_ERRS * 32];
+    for (int i = 0; i != 4; ++i) p.h[i] = sb[(F_BER_H0 + i) * 32];
+    for (int k = 0; k != 197; ++k) {
+        const uint32_t bit = (bert[k >> 3] >> (7 - (k & 7))) & 1u;
+        if (!p.synced) {                                              // synchronize(), :365-382
+            const uint32_t r = (bit ^ (p.state >> 8) ^ (p.state >> 4)) & 1u;
+            p.state = ((p.state << 1) | bit) & 0x1FFu;
+            if (r) p.sync_count = 0;
+            else if (++p.sync_count == 18u) {
+                p.synced = 1; p.bits += 18u;
+                p.h[0] = p.h[1] = p.h[2] = p.h[3] = 0;
+                p.hist_count = 0; p.hist_pos = 0; p.sync_count = 0;
+            }
+        } else {                                                      // generate() + count_errors(), :337-361
+            const uint32_t g = ((p.state >> 8) ^ (p.state >> 4)) & 1u;
+            p.state = ((p.state << 1) | g) & 0x1FFu;
+            const uint32_t err = bit ^ g;
+            p.bits += 1u;
+            const uint32_t wi = p.hist_pos >> 5, m = 1u << (p.hist_pos & 31u);
+            p.hist_count -= (p.h[wi] & m) ? 1u : 0u;
+            if (err) {
+                p.errs += 1u; p.hist_count += 1u; p.h[wi] |= m;
+                if (p.hist_count >= 25u) p.synced = 0;
+            } else p.h[wi] &= ~m;
+            if (++p.hist_pos == 128u) p.hist_pos = 0;
+        }
+    }
+    if ((w >> 30) & 1u) { prbs_reset(sb); return; }                   // the diagnostic callback of this very sample saw no carrier
+    sb[F_PRBS * 32] = p.state | (p.synced << 9) | (p.sync_count << 10) | ((p.hist_count & 0xFFu) << 15) | (p.hist_pos << 23);
+    sb[F_BER_BITS * 32] = p.bits; sb[F_BER_ERRS * 32] = p.errs;
+    for (int i = 0; i != 4; ++i) sb[(F_BER_H0 + i) * 32] = p.h[i];
+}
+
 // M17FrameDecoder::operator() for one lane whose framer has completed a frame.
 M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t head, unsigned long long head64)
 {
@@ -1916,6 +2037,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
             if (b111) { if (b109) dec_state = DEC_STREAM; }
             else dec_state = ((b109 << 1) | b110) == 1 ? DEC_BASIC_PACKET : DEC_FULL_PACKET;
             emit_record(d, s, sb, sample_pos, M17B_FRAME_LSF, (int) vcost);
+            consume_lsf(d, s, sb, bytes + 26 * np, np);
         } else {
             ctr_add(&d.ctr->lsf_crc_fail, 1ull);
             lich_segments = 0;
@@ -1944,6 +2066,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
                         dec_state = DEC_STREAM;
                         vcost = 0;
                         emit_record(d, s, sb, sample_pos, M17B_FRAME_LSF, 0);
+                        consume_lsf(d, s, sb, bytes + 26 * np, np);
                     } else {
                         vcost = 128;
                     }
@@ -1965,6 +2088,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
             for (int i = 0; i != 26; ++i) bytes[(size_t) i * np] = out[i];
             emit_record(d, s, sb, sample_pos,
                         dec_state == DEC_BASIC_PACKET ? M17B_FRAME_BASIC_PACKET : M17B_FRAME_FULL_PACKET, (int) vcost);
+            consume_packet(d, s, sb, out, sample_pos);
             if (out[25] & 0x80) dec_state = DEC_LSF;
         } else {
             dec_state = DEC_LSF;
@@ -1975,7 +2099,9 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
         vcost = viterbi(3, llr, np, stale, hcol, out);
         for (int i = 0; i != 25; ++i) bytes[(size_t) i * np] = out[i];
         emit_record(d, s, sb, sample_pos, M17B_FRAME_BERT, (int) vcost);
+        consume_bert(sb, out);
     }
+    if (swt != SW_BERT && (sb[F_PRBS * 32] >> 30) & 1u) prbs_reset(sb);    // (reset deferred behind this frame, see ber_diag_hook)
 
     sb[F_DEC * 32] = (uint32_t) dec_state | (lich_segments << 8) | ((uint32_t) (uint8_t) (int8_t) stale << 16);
     sb[F_VCOST * 32] = vcost;

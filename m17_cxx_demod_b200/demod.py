@@ -44,7 +44,19 @@ class Diag(ctypes.Structure):
 
 class Counters(ctypes.Structure):
     _fields_ = [("samples", ctypes.c_uint64), ("frames", ctypes.c_uint64 * 6), ("lsf_crc_fail", ctypes.c_uint64),
-                ("golay_fail", ctypes.c_uint64), ("faults", ctypes.c_uint64), ("dropped", ctypes.c_uint64)]
+                ("golay_fail", ctypes.c_uint64), ("faults", ctypes.c_uint64), ("dropped", ctypes.c_uint64),
+                ("packets_ok", ctypes.c_uint64), ("packets_crc_fail", ctypes.c_uint64), ("packet_seq_errors", ctypes.c_uint64),
+                ("packets_dropped", ctypes.c_uint64)]
+
+
+class Ber(ctypes.Structure):
+    _fields_ = [("synced", ctypes.c_int32), ("bits", ctypes.c_uint32), ("errors", ctypes.c_uint32), ("packet_bytes", ctypes.c_uint32)]
+
+
+PACKET_MAX = 860
+PACKET_DTYPE = np.dtype([("stream", "<u4"), ("seq", "<u4"), ("sample_pos", "<u8"), ("length", "<u2"), ("fcs_ok", "u1"), ("pad", "u1"),
+                         ("data", "u1", (PACKET_MAX,))])
+assert PACKET_DTYPE.itemsize == 880
 
 
 class Profile(ctypes.Structure):
@@ -83,7 +95,7 @@ def load_library() -> ctypes.CDLL:
                      "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_debug_correlate", "m17b_diag_drain",
                      "m17b_measure_fp32_peak",
                      "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count",
-                     "m17b_event_record", "m17b_event_elapsed", "m17b_profile_enable"):
+                     "m17b_event_record", "m17b_event_elapsed", "m17b_profile_enable", "m17b_packet_drain", "m17b_ber_get"):
             getattr(lib, name).restype = ctypes.c_int
         lib.m17b_submit.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int]
         lib.m17b_sync.argtypes = [ctypes.c_void_p]
@@ -112,6 +124,8 @@ def load_library() -> ctypes.CDLL:
                                              ctypes.c_void_p, ctypes.c_void_p]
         lib.m17b_diag_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
         lib.m17b_profile_enable.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.m17b_packet_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
+        lib.m17b_ber_get.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(Ber)]
         lib.m17b_event_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.m17b_event_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
         lib.m17b_measure_fp32_peak.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
@@ -267,6 +281,23 @@ class Demodulator:
         p = Profile()
         self._check(self._lib.m17b_get_profile(self._ctx, ctypes.byref(p), int(reset)), "m17b_get_profile")
         return p
+
+    def packet_drain(self) -> np.ndarray:
+        """All packet records (one per final packet segment decoded) since the last call, m17b_packet_drain."""
+        parts = []
+        while True:
+            buf = np.zeros(256, PACKET_DTYPE)
+            n = ctypes.c_size_t()
+            self._check(self._lib.m17b_packet_drain(self._ctx, buf.ctypes.data_as(ctypes.c_void_p), 256, ctypes.byref(n)), "m17b_packet_drain")
+            parts.append(buf[:n.value])
+            if n.value < 256:
+                break
+        return np.concatenate(parts)
+
+    def ber(self, stream: int) -> Ber:
+        b = Ber()
+        self._check(self._lib.m17b_ber_get(self._ctx, stream, ctypes.byref(b)), "m17b_ber_get")
+        return b
 
     def profile_enable(self, on: bool):
         self._check(self._lib.m17b_profile_enable(self._ctx, int(on)), "m17b_profile_enable")

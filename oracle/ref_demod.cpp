@@ -15,6 +15,8 @@
 // CPU baseline uses.
 
 #include "M17Demodulator.h"   // -I/root/reference/include/m17cxx -I/root/reference/blaze
+#include "ax25_frame.h"       // the reference's AX.25 printer (used by apps/m17-demod.cpp:224-229)
+#include <sstream>
 
 #include "m17_oracle.h"
 
@@ -299,6 +301,29 @@ void m17ref_correlate_trace(const float* in, size_t n, float* out5)
         out5[5 * i + 3] = c.correlate({3,-3,3,3,-3,-3,-3,-3});
         out5[5 * i + 4] = c.correlate({+3,+3,+3,+3,+3,+3,-3,+3});
     }
+}
+
+// ax25_frame.h:22-263: what apps/m17-demod.cpp:224-229 prints for a reassembled packet.  Returns the text length.
+size_t m17ref_ax25_print(const uint8_t* frame, size_t n, char* out, size_t cap)
+{
+    std::ostringstream os;
+    write(os, ax25_frame(std::string(reinterpret_cast<const char*>(frame), n)));
+    const std::string t = os.str();
+    if (cap) { const size_t k = t.size() < cap - 1 ? t.size() : cap - 1; std::memcpy(out, t.data(), k); out[k] = 0; }
+    return t.size();
+}
+
+// Util.h:320-413: PRBS9::validate over n bits (one per byte); `reset_before[i]` != 0 calls reset() first (what the
+// CLI's diagnostic callback does when it sees no carrier).  out = {synced, bit_count, err_count}.
+void m17ref_prbs9_validate(const uint8_t* bits, const uint8_t* reset_before, size_t n, uint32_t* out3)
+{
+    PRBS9 p;
+    p.history.fill(0);
+    for (size_t i = 0; i != n; ++i) {
+        if (reset_before && reset_before[i]) p.reset();
+        p.validate(bits[i] != 0);
+    }
+    out3[0] = p.synced; out3[1] = p.bit_count; out3[2] = p.err_count;
 }
 
 // KalmanFilter.h:18-66 + ClockRecovery.h:33-88.  ops[i]: 0 = reset(arg),

@@ -22,6 +22,7 @@
 #include <unistd.h>
 
 extern "C" size_t m17ref_demod_once(const int16_t*, size_t, unsigned, uint32_t, m17o_record*, size_t, m17o_trace*);
+extern "C" size_t m17ref_ax25_print(const uint8_t*, size_t, char*, size_t);
 extern "C" int m17ref_demod_batch(const int16_t*, size_t, size_t, size_t, unsigned, m17o_record*, size_t,
                                   uint64_t*, m17o_trace*, int);
 
@@ -49,6 +50,19 @@ int main(int argc, char** argv)
         else if (a == "--batch") batch = true;
         else if (a == "--quiet") quiet = true;
         else if (a == "--jobs" && i + 1 < argc) jobs = std::atoi(argv[++i]);
+        else if (a == "--ax25-print" && i + 1 < argc) {
+            // the reference's ax25_frame + write() (ax25_frame.h:22-263) on the bytes of a file, to stdout
+            std::FILE* f = std::fopen(argv[++i], "rb");
+            if (!f) return 2;
+            std::vector<uint8_t> bytes;
+            int ch;
+            while ((ch = std::fgetc(f)) != EOF) bytes.push_back(uint8_t(ch));
+            std::fclose(f);
+            std::vector<char> text(1 << 16);
+            size_t n = m17ref_ax25_print(bytes.data(), bytes.size(), text.data(), text.size());
+            std::fwrite(text.data(), 1, n < text.size() - 1 ? n : text.size() - 1, stdout);
+            return 0;
+        }
         else pos.push_back(a);
     }
 

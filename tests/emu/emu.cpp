@@ -35,7 +35,8 @@ struct Emu {
     std::vector<float2> ckpt_ring;
     std::vector<int16_t> llr, ring_x;
     std::vector<uint32_t> fix_list, dec_list, mask_ring;
-    std::vector<uint8_t> dec_bytes;
+    std::vector<uint8_t> dec_bytes, pkt_buf;
+    std::vector<m17b_packet> pkt_recs;
     std::vector<m17b_frame> recs;
     Counters ctr{};
     LlrTable tab{};
@@ -76,6 +77,10 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     m.llr.assign(184 * np, 0);
     m.dec_bytes.assign(56 * np, 0);
     m.recs.resize(d.rec_cap);
+    m.pkt_buf.assign(np * (size_t) kPktStride, 0);
+    d.pkt_cap = next_pow2(std::max<uint32_t>(64u, (uint32_t) np));
+    m.pkt_recs.resize(d.pkt_cap);
+    d.pkt_buf = m.pkt_buf.data(); d.pkt_recs = m.pkt_recs.data(); d.pkt_read = 0;
     d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_snap = m.corr_snap.data();
     d.mask_ring = m.mask_ring.data(); d.ckpt_ring = m.ckpt_ring.data(); d.seg_ring = m.seg_ring.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;

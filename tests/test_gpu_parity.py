@@ -9,6 +9,7 @@ import subprocess
 import numpy as np
 import pytest
 
+import consumers
 import m17_cxx_demod_b200 as m
 import oracle_lib as ol
 from m17_cxx_demod_b200 import gen
@@ -308,24 +309,69 @@ def test_cli_packet_reassembly_matches_reference_logic(tmp_path, encapsulated):
     assert sum(ol.TYPE_NAMES[int(r["type"])] in ("BASIC_PACKET", "FULL_PACKET") for r in want[0]) >= 5
     assert run.stdout == _reassemble_packets(want[0])
     if encapsulated == 0:
-        assert len(run.stdout) > 100 and b"FCS ok" in run.stderr      # one complete RAW packet
+        assert len(run.stdout) > 100 and b"Dest: " in run.stderr and b"Info: " in run.stderr      # one complete RAW packet, printed like the reference does
 
 
 def test_cli_bert_bit_error_rate_line(tmp_path):
-    """PRBS9 accounting over the decoded BERT frames (197 bits per frame, Util.h:320-413)."""
+    """PRBS9 accounting over the decoded BERT frames (197 bits per frame, Util.h:320-413), reset by
+    the diagnostic callback when it reports no carrier: the last BER line the CLI prints must show exactly the error and
+    bit counts the reference's logic gives on the reference's frames and diagnostic callbacks."""
     exe = os.path.join(ROOT, "m17_cxx_demod_b200", "m17-demod")
     x = gen.generate([gen.default_params(seed=304, mode=gen.BERT, snr_db=4.0, lead_in=3000, n_frames=24, repeat=1)], 96000)
     f = tmp_path / "b.s16"
     x[0].tofile(f)
     run = subprocess.run([exe, "-b"], stdin=open(f, "rb"), capture_output=True, check=True)
-    want, _ = ol.demod_batch("port", x, flags=2)
+    # the CLI loop's EOF quirk (apps/m17-demod.cpp:484-490): the last sample is processed twice
+    want, tr = ol.demod_batch("port", np.concatenate([x, x[:, -1:]], axis=1), trace=True)
     n_bert = sum(ol.TYPE_NAMES[int(r["type"])] == "BERT" for r in want[0])
     assert n_bert >= 10
+    _, _, printed = consumers.run_consumers(want[0], tr[0])
+    assert printed and printed[-1][1] > 1000
     import re
     lines = re.findall(rb"BER: ([0-9.]+) \((\d+) bits\)", run.stderr)
     assert lines, run.stderr[-400:]
-    ber, bits = float(lines[-1][0]), int(lines[-1][1])
-    assert 0 < bits <= 197 * n_bert and ber < 0.2
+    assert len(lines) == len(printed)
+    for (ber, bits), (e, n) in zip(lines, printed):
+        assert int(bits) == n and ber.decode() == "%-1.6f" % (e / n)
+
+
+def test_device_side_packet_and_ber_consumers():
+    """SURVEY 8(f) row 1 behind the C ABI: per-stream packet reassembly (sequence check, CRC-16/X.25 residue) and PRBS9
+    bit-error accounting run on the device after decode_kernel; m17b_packet_drain / m17b_ber_get / m17b_counters must
+    give what the reference CLI's logic gives on the reference's own frames and diagnostic callbacks, stream by stream."""
+    # (seeds / SNRs at which the reference acquires these synthetic transmissions, see DESIGN.md section 2; the BERT
+    # transmissions with odd seeds run to the end of the input, so that their accounting is live when it is queried)
+    pk = [1007, 1025, 1037, 1060, 1083, 1091, 1096, 1105, 1151, 1190]
+    ps = [gen.default_params(seed=s, mode=gen.PACKET, snr_db=4.0 + (s % 5), lead_in=3000 + 37 * (s % 50), n_frames=6 + (s % 20),
+                             repeat=1, gap=3000, packet_encapsulated=s % 2) for s in pk]
+    ps += [gen.default_params(seed=s, mode=gen.BERT, snr_db=4.0 + (s % 5), lead_in=3000 + 37 * (s % 50),
+                              n_frames=0 if s % 2 else 6 + (s % 20), tail=0 if s % 2 else 4800, repeat=1, gap=3000) for s in range(2000, 2020)]
+    ps += [gen.default_params(seed=s, mode=gen.MIXED, snr_db=4.0 + (s % 5), lead_in=3000 + 37 * (s % 50), repeat=1, gap=3000,
+                              packet_encapsulated=s % 2) for s in range(3000, 3018)]
+    x = gen.generate(ps, 120000)
+    want, tr = ol.demod_batch("port", x, trace=True)
+    with m.Demodulator(48, 9600, flags=m.STREAMING) as d:
+        got = d.demodulate(x, chunk=9600)
+        pk = d.packet_drain()
+        bers = [d.ber(s) for s in range(48)]
+        c = d.counters()
+    assert_records_match(want, got, "consumers corpus")
+    n_ok = n_bad = n_seq = n_synced = 0
+    for s in range(48):
+        P, R, _ = consumers.run_consumers(want[s], tr[s])
+        mine = pk[pk["stream"] == s]
+        assert len(mine) == len(P.done), f"stream {s}: {len(mine)} packet records, reference logic completes {len(P.done)}"
+        assert list(mine["seq"]) == list(range(len(mine)))
+        for r, (pos, ok, data) in zip(mine, P.done):
+            assert int(r["sample_pos"]) == pos and bool(r["fcs_ok"]) == ok and int(r["length"]) == len(data)
+            assert bytes(r["data"][:len(data)]) == data
+            n_ok += ok; n_bad += not ok
+        n_seq += P.seq_errors
+        b = bers[s]
+        assert (bool(b.synced), b.bits, b.errors, b.packet_bytes) == (R.synced, R.bit_count, R.err_count, len(P.cur)), f"stream {s}"
+        n_synced += int(R.synced and R.bit_count > 0)
+    assert (c.packets_ok, c.packets_crc_fail, c.packet_seq_errors, c.packets_dropped) == (n_ok, n_bad, n_seq, 0)
+    assert n_ok >= 3 and n_bad >= 3 and n_synced >= 5, (n_ok, n_bad, n_seq, n_synced)
 
 
 def _expected_diagnostics(tr):
