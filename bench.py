@@ -80,6 +80,9 @@ def parse_args():
     ap.add_argument("--channels", type=int, default=0, help="channels per GPU (default: workload's)")
     ap.add_argument("--chunk", type=int, default=9600, help="samples per channel per step")
     ap.add_argument("--unique", type=int, default=1024, help="unique waveforms tiled over the channels")
+    ap.add_argument("--gen", default="cpu", choices=["cpu", "device"],
+                    help="device: the waveforms are built on the GPU by the device-side modulator (bit-identical to the CPU "
+                         "generator; makes --unique up to the channel count practical: every channel its own waveform)")
     ap.add_argument("--fma", action="store_true", help="fused multiply-add matched filter (not bit-identical)")
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-e2e", action="store_true")
@@ -239,11 +242,22 @@ def main():
 
     # ---- synthetic input: U unique waveforms generated on the CPU, tiled on the device -------
     t0 = time.perf_counter()
-    uniq = gen.generate(w.params, total)
-    gen_s = time.perf_counter() - t0
-    uniq_d = torch.from_numpy(uniq).to(dev)
-    idx = (torch.arange(lo, hi, device=dev) % U)
-    big = uniq_d.index_select(0, idx)                          # [channels][total] int16 resident in HBM
+    if args.gen == "device":
+        # every waveform built on the GPU (csrc/m17gen_dev.cu); the host copy is only for the parity leg and e2e
+        uniq_d = torch.empty((U, total), dtype=torch.int16, device=dev)
+        gen.generate_device(w.params, total, uniq_d.data_ptr(), device=local)
+        torch.cuda.synchronize()
+        gen_s = time.perf_counter() - t0
+        uniq = uniq_d.cpu().numpy()
+    else:
+        uniq = gen.generate(w.params, total)
+        gen_s = time.perf_counter() - t0
+        uniq_d = torch.from_numpy(uniq).to(dev)
+    if U == channels and lo % U == 0:
+        big = uniq_d                                           # every channel its own waveform
+    else:
+        idx = (torch.arange(lo, hi, device=dev) % U)
+        big = uniq_d.index_select(0, idx)                      # [channels][total] int16 resident in HBM
     assert big.is_contiguous()
     torch.cuda.synchronize()
 
@@ -372,6 +386,7 @@ def main():
                    "l2": f"inputs larger than L2 ({channels * T * 2 / 1e6:.0f} MB of int16 per step, never re-read)",
                    "drain": "records of step k read back (m17b_drain_upto) while step k+1 runs; all inside the timed region",
                    "mode": "M17B_STREAMING (streams walk whole frames; every frame ending in a step is delivered with that step)",
+                   "generator": "device-side modulator (csrc/m17gen_dev.cu)" if args.gen == "device" else "CPU generator (csrc/m17gen.cpp)",
                    "generator_s": round(gen_s, 2), **({"no_overlap": True} if args.no_overlap else {})},
         "frames_per_s": totals["frames"] / t_max, "wall_s": t_wall, "device_s": t_dev,
         "roofline": {"bound": "fp32", "kernel": "fir_kernel", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",

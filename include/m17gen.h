@@ -10,7 +10,8 @@
  * M17Demodulator.h:156), and applies seeded channel impairments (AWGN, symbol
  * clock skew, DC offset == the demodulator's "frequency offset").
  *
- * It is CPU code and is not on the demodulation path.
+ * libm17gen.so is CPU code; libm17gen_cuda.so (m17gen_batch_device) builds the same waveforms on the GPU.
+ * Neither is on the demodulation path.
  */
 #ifndef M17GEN_H
 #define M17GEN_H
@@ -65,6 +66,16 @@ int m17gen_stream(const m17gen_params* p, int16_t* out, size_t n_samples, m17gen
 /* n_streams streams, params[i] each, out[i*stride ...]; n_threads host threads. */
 int m17gen_batch(const m17gen_params* params, size_t n_streams, int16_t* out, size_t n_samples,
                  size_t stride, m17gen_truth* truth /* may be NULL */, int n_threads);
+
+/* 10^(snr_db / 20) as the generator computes it (host libm; the device-side build takes it as an input). */
+double m17gen_snr_linear(float snr_db);
+
+/* Device-side modulator (libm17gen_cuda.so, csrc/m17gen_dev.cu): the same n_streams streams written to device
+ * memory out_device[i * stride ...] on CUDA device `device`, bit-identical to m17gen_batch for the same
+ * parameters.  params and snr_linear (one m17gen_snr_linear(params[i].snr_db) per stream) are host arrays.
+ * Returns 0 on success. */
+int m17gen_batch_device(const m17gen_params* params, const double* snr_linear, size_t n_streams,
+                        int16_t* out_device, size_t n_samples, size_t stride, int device);
 
 /* Building blocks, exposed so tests can pin them against the reference's KATs. */
 uint16_t m17gen_crc16(const uint8_t* data, size_t n);               /* CRC16.h, poly 0x5935 */

@@ -79,6 +79,35 @@ def generate(params: list[GenParams], n_samples: int, n_threads: int | None = No
     return out
 
 
+_cuda_lib = None
+
+
+def cuda_lib() -> ctypes.CDLL:
+    """libm17gen_cuda.so: the device-side modulator (csrc/m17gen_dev.cu)."""
+    global _cuda_lib
+    if _cuda_lib is None:
+        path = os.path.join(_HERE, "libm17gen_cuda.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        _cuda_lib = ctypes.CDLL(path)
+        _cuda_lib.m17gen_batch_device.restype = ctypes.c_int
+    return _cuda_lib
+
+
+def generate_device(params: list[GenParams], n_samples: int, out_ptr: int, stride: int | None = None, device: int = 0) -> None:
+    """Build len(params) streams of n_samples int16 ON THE GPU into device memory at out_ptr (stream i at
+    out_ptr + 2 * i * stride): the same samples `generate` gives, bit for bit."""
+    n = len(params)
+    arr = (GenParams * n)(*params)
+    lib().m17gen_snr_linear.restype = ctypes.c_double
+    lib().m17gen_snr_linear.argtypes = [ctypes.c_float]
+    snr = np.array([lib().m17gen_snr_linear(p.snr_db) for p in params], np.float64)
+    rc = cuda_lib().m17gen_batch_device(arr, snr.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(n), ctypes.c_void_p(out_ptr),
+                                        ctypes.c_size_t(n_samples), ctypes.c_size_t(stride or n_samples), ctypes.c_int(device))
+    if rc:
+        raise RuntimeError(f"m17gen_batch_device failed: {rc}")
+
+
 @dataclass
 class Workload:
     """A named synthetic corpus (SURVEY.md section 8d / BASELINE.json configs)."""

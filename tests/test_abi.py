@@ -29,9 +29,9 @@ def test_libm17b_exports_every_declared_symbol():
 
 def test_libm17gen_exports_every_declared_symbol():
     from m17_cxx_demod_b200 import gen
-    lib = gen.lib()
+    lib, cuda = gen.lib(), gen.cuda_lib()          # (the device-side modulator has its own library; loading needs no GPU)
     for n in declared("m17gen.h", "m17gen_"):
-        assert hasattr(lib, n), f"libm17gen.so does not export {n}"
+        assert hasattr(cuda if n == "m17gen_batch_device" else lib, n), f"libm17gen(_cuda).so does not export {n}"
 
 
 def test_signatures_use_plain_c_types_only():
