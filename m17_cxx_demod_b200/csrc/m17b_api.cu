@@ -152,6 +152,7 @@ int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard, uint32_t
         ev_begin(c, s, CAT_DECODE, p);
         launch_decode(c->d, c->head, c->head64, cls, s);
         ev_end(c, s, p);
+        c->prof.decode_launches += 1;
         if (cls) {                   // (a receiving stream that needs fixup_kernel becomes class 1 first, see scan_lane)
             ev_begin(c, s, CAT_FIXUP, p);
             launch_fixup(c->d, c->head, c->sm_count, cls, s);
@@ -159,7 +160,6 @@ int run_round(m17b_ctx* c, bool defer, cudaStream_t st, uint32_t guard, uint32_t
             c->prof.fixup_launches += 4;
         }
         c->prof.scan_launches += 1;
-        c->prof.decode_launches += 1;
     }
     c->prof.scan_launches += 1;      // classify_kernel
     if (fork) {
@@ -451,8 +451,7 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
     // doubled it writes no ring position a lane of the previous submit still reads (ring guard in scan_lane).
     // It may be one submit ahead of the rounds, not two.
     const bool streaming = (c->cfg.flags & M17B_STREAMING) != 0;
-    static const bool no_front = getenv("M17B_NO_FRONT") != nullptr;      // experiment: front end in line with the rounds
-    cudaStream_t fs = streaming && !no_front ? c->front : c->compute;
+    cudaStream_t fs = streaming ? c->front : c->compute;
     if (streaming) {                                                                    // rounds of submit k-2, both chains
         CK(cudaStreamWaitEvent(fs, c->ev_rounds[c->n_submits & 1], 0));
         CK(cudaStreamWaitEvent(fs, c->ev_aux_rounds[c->n_submits & 1], 0));
@@ -523,8 +522,7 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
             int rc = run_round(c, true, c->compute, guard, 1u);
             if (rc != M17B_OK) return rc;
         }
-        static const int aux_rounds = getenv("M17B_AUX_ROUNDS") ? atoi(getenv("M17B_AUX_ROUNDS")) : 0;     // experiment
-        for (int r = 0; r != (aux_rounds ? aux_rounds : rounds); ++r) {
+        for (int r = 0; r != rounds; ++r) {
             int rc = run_round(c, true, c->aux, guard, 2u);
             if (rc != M17B_OK) return rc;
         }

@@ -230,8 +230,6 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
     uint32_t span = head + n_new - b0;
     dim3 grid(d.np / kFirStreams, (span + kFirTile - 1) / kFirTile);
     size_t smem = sizeof(float) * kFirStreams * kFirRow;
-    static const int pad_kb = getenv("M17B_FIR_PAD_KB") ? atoi(getenv("M17B_FIR_PAD_KB")) : 0;     // experiment: fewer CTAs per SM
-    smem += (size_t) pad_kb * 1024;
     // 16-byte loads need the chunk to start on a ring-chunk boundary and 16-byte aligned rows
     int aligned = (head % 8 == 0) && (stride % 8 == 0) && (reinterpret_cast<uintptr_t>(in) % 16 == 0) &&
                   (reinterpret_cast<uintptr_t>(tail) % 16 == 0);
@@ -620,11 +618,12 @@ cudaError_t configure_kernels()
     cudaError_t e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int) (sizeof(uint16_t) * 244 * kDecThreads));
     if (e != cudaSuccess) return e;
+
     e = cudaFuncSetAttribute(fir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int) (sizeof(float) * kFirStreams * kFirRow) + 64 * 1024);
+                             (int) (sizeof(float) * kFirStreams * kFirRow));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(fir_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int) (sizeof(float) * kFirStreams * kFirRow) + 64 * 1024);
+                                (int) (sizeof(float) * kFirStreams * kFirRow));
 }
 
 __global__ void init_state_kernel(DevPtrs d, uint32_t origin)

@@ -1754,7 +1754,7 @@ M17B_FN void butterfly2(const uint32_t (&m)[8], uint32_t (&n)[8], uint32_t& hist
 // Viterbi.h:181-236.  Writes out_bits(kind) bits MSB-first into out[] (to_byte_array,
 // Util.h:300-318) and returns round(min_metric / 7.f).
 M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale,
-                              uint16_t* hist_col /* stride HS */, uint8_t* out)
+                              uint16_t* hist_col, int hs /* survivor-history stride */, uint8_t* out)
 {
     const int16_t* map = M17B_TAB.vmap[kind];
     const int n_in = map_len(kind), n_out = out_bits(kind), steps = n_in / 2;
@@ -1802,7 +1802,7 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
             butterfly2<2>(m, n, h, pb, pc); butterfly2<3>(m, n, h, pa, pd);
             butterfly2<4>(m, n, h, pc, pb); butterfly2<5>(m, n, h, pd, pa);
             butterfly2<6>(m, n, h, pd, pa); butterfly2<7>(m, n, h, pc, pb);
-            hist_col[t * HS] = (uint16_t) h;
+            hist_col[t * hs] = (uint16_t) h;
 #pragma unroll
             for (int i = 0; i != 8; ++i) m[i] = n[i];
 #else
@@ -1810,7 +1810,7 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
             butterfly<2>(m, n, h, a0, a1, b0, b1); butterfly<3>(m, n, h, a0, a1, b0, b1);
             butterfly<4>(m, n, h, a0, a1, b0, b1); butterfly<5>(m, n, h, a0, a1, b0, b1);
             butterfly<6>(m, n, h, a0, a1, b0, b1); butterfly<7>(m, n, h, a0, a1, b0, b1);
-            hist_col[t * HS] = (uint16_t) h;
+            hist_col[t * hs] = (uint16_t) h;
 #pragma unroll
             for (int i = 0; i != 16; ++i) m[i] = n[i];
 #endif
@@ -1835,7 +1835,7 @@ M17B_FN_COLD uint32_t viterbi(int kind, const int16_t* llr, size_t np, int stale
     for (int i = 0; i != n_bytes; ++i) out[i] = 0;
     int next = min_element, index = steps, o = n_out;
     for (int t = steps; t-- != 0 && o != 0;) {
-        int v = (hist_col[t * HS] >> next) & 1;      // prevState_[next][v] = (next >> 1) | (v << 3)
+        int v = (hist_col[t * hs] >> next) & 1;      // prevState_[next][v] = (next >> 1) | (v << 3)
         if (index-- <= n_out) { --o; out[o >> 3] |= (uint8_t) ((next & 1) << (7 - (o & 7))); }
         next = (next >> 1) | (v << 3);
     }
@@ -2004,7 +2004,7 @@ M17B_FN_COLD void consume_bert(uint32_t* sb, const uint8_t* bert /* 25 bytes */)
 }
 
 // M17FrameDecoder::operator() for one lane whose framer has completed a frame.
-M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t head, unsigned long long head64)
+M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t head, unsigned long long head64, int hs = HS)
 {
     uint32_t* sb = d.st + st_index(s, 0);
     uint32_t fl = sb[F_FLAGS * 32];
@@ -2028,7 +2028,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
     if (swt == SW_LSF) {
         dec_state = DEC_LSF;
         // decode_lsf, :154-178
-        vcost = viterbi(0, llr, np, stale, hcol, out);
+        vcost = viterbi(0, llr, np, stale, hcol, hs, out);
         stale = soft_bit(llr, np, M17B_TAB.vmap[0][401], 0);              // depuncture_buffer.lsf[401]
         for (int i = 0; i != 30; ++i) bytes[(size_t) (26 + i) * np] = out[i];
         if (crc16_lsf(bytes + 26 * np, np) == 0) {
@@ -2074,7 +2074,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
             }
         } else if (dec_state == DEC_STREAM) {
             // decode_stream, :276-289
-            vcost = viterbi(1, llr, np, stale, hcol, out);
+            vcost = viterbi(1, llr, np, stale, hcol, hs, out);
             for (int i = 0; i != 18; ++i) bytes[(size_t) i * np] = out[i];
             emit_record(d, s, sb, sample_pos, M17B_FRAME_STREAM, (int) vcost);
         } else {
@@ -2083,7 +2083,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
     } else if (swt == SW_PACKET) {
         if (dec_state == DEC_BASIC_PACKET || dec_state == DEC_FULL_PACKET) {
             // decode_packet, :299-315
-            vcost = viterbi(2, llr, np, stale, hcol, out);
+            vcost = viterbi(2, llr, np, stale, hcol, hs, out);
             stale = soft_bit(llr, np, M17B_TAB.vmap[2][401], 0);          // depuncture_buffer.packet[401]
             for (int i = 0; i != 26; ++i) bytes[(size_t) i * np] = out[i];
             emit_record(d, s, sb, sample_pos,
@@ -2096,7 +2096,7 @@ M17B_FN void decode_lane(const DevPtrs& d, uint32_t s, uint16_t* hcol, uint32_t 
     } else {
         // decode_bert, :264-274
         dec_state = DEC_BERT;
-        vcost = viterbi(3, llr, np, stale, hcol, out);
+        vcost = viterbi(3, llr, np, stale, hcol, hs, out);
         for (int i = 0; i != 25; ++i) bytes[(size_t) i * np] = out[i];
         emit_record(d, s, sb, sample_pos, M17B_FRAME_BERT, (int) vcost);
         consume_bert(sb, out);
