@@ -88,6 +88,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--parity-waveforms", type=int, default=4096, help="unique waveforms the reference checks in the parity leg")
     ap.add_argument("--no-overlap", action="store_true",
                     help="diagnostic: wait for every step's own records before the next submit (no step overlaps the next)")
     ap.add_argument("--ref-streams", type=int, default=1024, help="streams per step of the reference arm")
@@ -418,7 +419,9 @@ def main():
     if rank == 0 and not args.no_parity:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_lib as ol
-        n_chk = U                                              # every waveform, hence every channel
+        # every waveform, hence every channel -- up to --parity-waveforms of them: the reference demodulates about one
+        # million samples per second and core, so 65,536 unique waveforms would take it ten minutes
+        n_chk = min(U, args.parity_waveforms)
         want, _ = ol.demod_batch("ref" if ol.have_ref() else "port", uniq[:n_chk, :])
         allrec = np.concatenate(records) if records else np.zeros(0, m.FRAME_DTYPE)
         per = m.demod.split_by_stream(allrec, channels)

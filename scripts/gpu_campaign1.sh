@@ -2,7 +2,7 @@
 # single-metric launch list, ncu --set full captures (matched filter with source; the other kernels; the scan with source)
 tag=${1:-r3}
 mkdir -p gpurun_out
-b() { name=$1; shift; timeout 1200 python bench.py "$@" > gpurun_out/${tag}_bench_${name}.json 2> gpurun_out/${tag}_bench_${name}.err; echo "bench ${name} exit $?"; }
+b() { name=$1; shift; timeout 400 python bench.py "$@" > gpurun_out/${tag}_bench_${name}.json 2> gpurun_out/${tag}_bench_${name}.err; echo "bench ${name} exit $?"; }
 b default
 b d20 --steps 20 --warmup 5 --no-cpu-baseline
 b reference --impl reference
@@ -10,7 +10,7 @@ b c2 --workload c2 --steps 20 --warmup 5 --no-cpu-baseline
 b c4 --workload c4 --steps 20 --warmup 5 --no-cpu-baseline
 b fma --fma --steps 30 --warmup 5 --no-cpu-baseline --no-e2e
 b 128k --channels 131072 --steps 20 --warmup 5 --no-cpu-baseline --no-e2e
-b unique65536 --gen device --unique 65536 --steps 10 --warmup 3 --no-cpu-baseline --no-e2e
+b unique65536 --gen device --unique 65536 --parity-waveforms 2048 --steps 10 --warmup 3 --no-cpu-baseline --no-e2e
 python - <<PY
 import json,glob
 for f in sorted(glob.glob("gpurun_out/${tag}_bench_*.json")):
@@ -20,6 +20,6 @@ for f in sorted(glob.glob("gpurun_out/${tag}_bench_*.json")):
 PY
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2400 --csv --log-file gpurun_out/${tag}_launches.csv python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_launch.log 2>&1; echo "launch list exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:fir_kernel -s 8 -c 1 -o gpurun_out/${tag}_fir python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_fir.log 2>&1; echo "ncu fir exit $?"
-timeout 1200 ncu --set full --clock-control none -k regex:'dcd_kernel|classify_kernel|decode_kernel|search_|fixup|tail_kernel' -s 500 -c 60 -o gpurun_out/${tag}_others python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_others.log 2>&1; echo "ncu others exit $?"
+timeout 1200 ncu --set full --clock-control none -k regex:'dcd_kernel|classify_kernel|decode_kernel|search_|fixup|tail_kernel' -s 500 -c 22 -o gpurun_out/${tag}_others python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_others.log 2>&1; echo "ncu others exit $?"
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:scan_kernel -s 112 -c 10 -o gpurun_out/${tag}_scan python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_scan.log 2>&1; echo "ncu scan exit $?"
 ls -la gpurun_out/*.ncu-rep
