@@ -1,5 +1,4 @@
-# usage: bash scripts/gpu_campaign1.sh <tag>  -- single-GPU measurement campaign: bench lines of every workload, both arms,
-# single-metric launch list, ncu --set full captures (matched filter with source; the other kernels; the scan with source)
+# usage: bash scripts/gpu_campaign1.sh <tag>  -- single-GPU bench lines of every workload, both arms (JSON lines only)
 tag=${1:-r3}
 mkdir -p gpurun_out
 b() { name=$1; shift; timeout 400 python bench.py "$@" > gpurun_out/${tag}_bench_${name}.json 2> gpurun_out/${tag}_bench_${name}.err; echo "bench ${name} exit $?"; }
@@ -18,8 +17,3 @@ for f in sorted(glob.glob("gpurun_out/${tag}_bench_*.json")):
     except Exception as e: print(f, "unreadable", e); continue
     print(f.split("_bench_")[1], round(d["value"]), round(d["ms_per_step"],2), d.get("parity",{}).get("mismatching"), d.get("parity",{}).get("records_compared"), d.get("faults"), "e2e", round(d.get("e2e",{}).get("value",0)), "frac", d.get("roofline",{}).get("frac"))
 PY
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2400 --csv --log-file gpurun_out/${tag}_launches.csv python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_launch.log 2>&1; echo "launch list exit $?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:fir_kernel -s 8 -c 1 -o gpurun_out/${tag}_fir python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_fir.log 2>&1; echo "ncu fir exit $?"
-timeout 1200 ncu --set full --clock-control none -k regex:'dcd_kernel|classify_kernel|decode_kernel|search_|fixup|tail_kernel' -s 500 -c 22 -o gpurun_out/${tag}_others python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_others.log 2>&1; echo "ncu others exit $?"
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:scan_kernel -s 112 -c 10 -o gpurun_out/${tag}_scan python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-parity > gpurun_out/${tag}_ncu_scan.log 2>&1; echo "ncu scan exit $?"
-ls -la gpurun_out/*.ncu-rep
