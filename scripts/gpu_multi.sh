@@ -1,11 +1,13 @@
-# usage: bash scripts/gpu_multi.sh <tag> <N> [second-workload]  -- the driver's N-GPU launch of both arms
-# (configs[2] workload), then optionally our arm once more on another workload (e.g. c4 = configs[3])
-tag=${1:-r01m}; N=${2:-2}; W2=${3:-}
+# usage: bash scripts/gpu_multi.sh <tag> <n_gpus> <name> [bench args]  -- one bench line on N GPUs of this box (torchrun, one rank per GPU)
+tag=$1; n=$2; name=$3; shift 3
 mkdir -p gpurun_out
-nvidia-smi -L | head -8; free -g | head -2; nproc
-run() { timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 bench.py --gpus $N "${@:3}" > gpurun_out/${tag}_$2_n$N.json 2> gpurun_out/${tag}_$2_n$N.err; echo "$2 exit $?"; }
-run 29511 ref --impl reference --steps 2 --warmup 1
-run 29512 bench --steps 10 --warmup 3
-[ -n "$W2" ] && run 29513 bench_$W2 --steps 10 --warmup 3 --workload $W2 --no-cpu-baseline
-tail -3 gpurun_out/${tag}_bench_n$N.err
-for f in gpurun_out/${tag}_bench*_n$N.json gpurun_out/${tag}_ref_n$N.json; do echo "== $f"; cut -c1-2500 $f; done
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n "$@" \
+  > gpurun_out/${tag}_bench_${name}_n${n}.json 2> gpurun_out/${tag}_bench_${name}_n${n}.err; echo "bench ${name} n=$n exit $?"
+tail -c 600 gpurun_out/${tag}_bench_${name}_n${n}.err
+python - <<PY
+import json
+try:
+    d=json.loads([l for l in open("gpurun_out/${tag}_bench_${name}_n${n}.json") if l.startswith("{")][-1])
+    print(round(d["value"]), round(d["ms_per_step"],2), d.get("parity"), d.get("faults"), d.get("dropped"), "e2e", d.get("e2e",{}).get("value"))
+except Exception as e: print("no line", e)
+PY
