@@ -48,6 +48,7 @@ extern "C" {
                               per loss, the surviving records stay drainable: drain more often / raise
                               frame_capacity                                       */
 #define M17B_ESTATE   -6   /* internal invariant violated (counter `faults`)       */
+#define M17B_ETOOBIG  -7   /* size beyond the fixed scratch of m17b_filter_noalloc (M17B_NOALLOC_MAX_*) */
 
 /* m17b_config.flags */
 #define M17B_FIR_FMA     0x1u  /* matched filter accumulates with fused multiply-add: outputs within
@@ -266,6 +267,24 @@ int  m17b_debug_filter(m17b_ctx* ctx, const int16_t* samples_host, size_t n, siz
  * (M17Demodulator.h:154-157), computed by the arithmetic the sync-word search pass uses. */
 int  m17b_debug_correlate(m17b_ctx* ctx, const int16_t* samples_host, size_t n, size_t stream_stride,
                           float* filtered_host /* [n_streams][n] */, float* corr_host /* [n_streams][n][5] */);
+
+/*
+ * No counterpart in the reference.  The matched filter of
+ * m17b_debug_filter (scaling + 150-tap RRC, zero history, filter mode from `flags`: 0, M17B_FIR_FMA, M17B_INVERT) for
+ * callers that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.
+ * It calls no cudaMalloc / cudaFree / allocating routine and needs no m17b_ctx: the kernel's scratch (its temporary
+ * sample ring, 5,283,840 bytes) is a static __device__ array that every GPU which loads the library holds until exit.
+ * Hence the limits: n_streams <= M17B_NOALLOC_MAX_STREAMS and n <= M17B_NOALLOC_MAX_SAMPLES, beyond which it returns
+ * M17B_ETOOBIG (use m17b_debug_filter).  Inputs and outputs are the caller's DEVICE buffers on `device`:
+ * samples_device[s * stream_stride + 0 .. n) int16, filtered_device [n_streams][n] float.  The work is enqueued on
+ * `cuda_stream` (a cudaStream_t; NULL = the default stream) and the call returns without waiting for it.  All calls on
+ * one GPU share the scratch array (it keeps the last call's contents; what must start at zero is cleared in every
+ * call): calls that overlap on the same GPU race -- serialise them, e.g. by using one stream.
+ */
+#define M17B_NOALLOC_MAX_STREAMS 128u
+#define M17B_NOALLOC_MAX_SAMPLES 4000u
+int  m17b_filter_noalloc(int device, const int16_t* samples_device, uint32_t n_streams, size_t n, size_t stream_stride,
+                         float* filtered_device, uint32_t flags, void* cuda_stream);
 
 /* FP32 pipe microbenchmark: sustained FFMA throughput of the context's GPU in TFLOP/s
  * (2 flop per FMA), the denominator of the matched filter's roofline fraction.

@@ -266,6 +266,7 @@ const char* m17b_strerror(int code)
     case M17B_ECUDA: return "CUDA error";
     case M17B_EOVERFLOW: return "frame record ring overflow";
     case M17B_ESTATE: return "internal state error";
+    case M17B_ETOOBIG: return "size exceeds the static scratch of m17b_filter_noalloc (at most 128 streams x 4000 samples per call)";
     default: return "unknown error";
     }
 }

@@ -95,7 +95,7 @@ def load_library() -> ctypes.CDLL:
                      "m17b_counters_get", "m17b_get_profile", "m17b_debug_filter", "m17b_debug_correlate", "m17b_diag_drain",
                      "m17b_measure_fp32_peak",
                      "m17b_host_alloc", "m17b_device_alloc", "m17b_memcpy_h2d", "m17b_device_count",
-                     "m17b_event_record", "m17b_event_elapsed", "m17b_profile_enable", "m17b_packet_drain", "m17b_ber_get"):
+                     "m17b_event_record", "m17b_event_elapsed", "m17b_profile_enable", "m17b_packet_drain", "m17b_ber_get", "m17b_filter_noalloc"):
             getattr(lib, name).restype = ctypes.c_int
         lib.m17b_submit.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int]
         lib.m17b_sync.argtypes = [ctypes.c_void_p]
@@ -123,6 +123,8 @@ def load_library() -> ctypes.CDLL:
         lib.m17b_debug_correlate.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
                                              ctypes.c_void_p, ctypes.c_void_p]
         lib.m17b_diag_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
+        lib.m17b_filter_noalloc.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_size_t, ctypes.c_size_t,
+                                            ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p]
         lib.m17b_profile_enable.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.m17b_packet_drain.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
         lib.m17b_ber_get.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(Ber)]
