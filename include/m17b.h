@@ -229,7 +229,9 @@ int  m17b_drain(m17b_ctx* ctx, m17b_frame* out, size_t cap, size_t* n);
  * later submits keep running -- and returns the records appended up to then (same ordering rules as
  * m17b_drain; a stream that had not reached the end of that submit yet delivers the rest with a later
  * ticket or with m17b_drain).  The device-to-host transfer runs on the copy stream beside the kernels of
- * the later submits.  Keep at most 8 submits in flight. */
+ * the later submits.  Keep at most 8 submits in flight -- and size m17b_config.frame_capacity for the depth you use: the
+ * default holds the worst case of three submits (the one being drained and two enqueued behind it).  When the ring does
+ * overflow, the surviving records stay drainable and M17B_EOVERFLOW is returned once per loss (counter `dropped`). */
 unsigned long long m17b_ticket(const m17b_ctx* ctx);
 int  m17b_drain_upto(m17b_ctx* ctx, unsigned long long ticket, m17b_frame* out, size_t cap, size_t* n);
 
