@@ -46,7 +46,7 @@ struct Emu {
 
 uint32_t g_origin = 0;       // ring position of the first sample (wrap-around tests)
 
-void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
+void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap, uint32_t ring_submits = 1)
 {
     static bool tables = false;
     if (!tables) { build_tables(h_tab, h_golay); tables = true; }
@@ -57,7 +57,7 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap)
     DevPtrs& d = m.d;
     d.n_streams = n_streams;
     d.np = (n_streams + 127u) & ~127u;
-    d.ring_lines = next_pow2((max_chunk + kRoundCap + 160 + 16 + kLine - 1) / kLine + 1);
+    d.ring_lines = next_pow2((max_chunk * ring_submits + kRoundCap + 160 + 16 + kLine - 1) / kLine + 1);
     d.rec_cap = next_pow2((uint32_t) rec_cap);
     d.rec_read = 0;
     size_t np = d.np;
@@ -117,6 +117,50 @@ void round(Emu& m, bool defer)
     }
 }
 
+// ---- M17B_STREAMING's two independent chains of rounds (m17b_api.cu: run_round with mask 1 / 2) -----------------
+// classify_kernel's decision for one stream (m17b_kernels.cu; restated here because that kernel is warp code):
+// the walk class the stream is listed in for a round of the chain `mask` (1 = receiving, 2 = acquiring), or -1.
+int classify(const DevPtrs& d, uint32_t s, uint32_t head, uint32_t mask, bool defer, Counters& ctr)
+{
+    const uint32_t* sb = d.st + st_index(s, 0);
+    const uint32_t fl = sb[F_FLAGS * 32], pos = sb[F_POS * 32];
+    const int own = (mask & 1u) ? 0 : 1;
+    if ((int32_t) (head - pos) <= 0) return -1;
+    if (fl & (FL_PENDING | FL_FIXUP)) { ctr.cls[own].lagging += 1; return -1; }
+    const int st = (int) ((fl >> FL_STATE_SHIFT) & 7);
+    const bool receiving = (fl & FL_DCD) && (sb[F_CNT * 32] >> 16) == 0 && (sb[F_IDX * 32] >> 24) >= (uint32_t) kTapsUsed &&
+                           (st == ST_FRAME || st == ST_STREAM_SYNC || st == ST_PACKET_SYNC || st == ST_BERT_SYNC || st == ST_SYNC_WAIT);
+    const int cls = receiving ? 0 : 1;
+    if (!((mask >> cls) & 1u)) return -1;
+    if (defer && defers_at_once(sb, fl, pos, head)) { ctr.cls[own].deferred += 1; return -1; }
+    return cls;
+}
+
+struct Task { int chain; uint32_t head; unsigned long long head64; uint32_t submit; };
+
+// one round of one chain, as run_round(mask = 1 << chain) enqueues it
+void chain_round(Emu& m, const Task& t, uint32_t guard)
+{
+    DevPtrs& d = m.d;
+    const int c = t.chain;
+    m.ctr.cls[c] = ClassCounters{};
+    std::vector<uint32_t> list;
+    for (uint32_t s = 0; s != d.n_streams; ++s)
+        if (classify(d, s, t.head, 1u << c, true, m.ctr) == c) list.push_back(s);
+    for (uint32_t s : list) scan_lane(d, make_io(d, s, &m.tab, c, c == 1), t.head, t.head64, true, true, guard);
+    uint16_t hist[244];
+    for (int k = 0; k != 5; ++k)
+        for (uint32_t q = 0; q != m.ctr.cls[c].dec_count[k]; ++q)
+            decode_lane(d, m.dec_list[(size_t) (c * 5 + k) * d.np + q], hist, t.head, t.head64);
+    if (c == 1)
+        for (uint32_t q = 0; q != m.ctr.cls[1].fix_count; ++q) {
+            const uint32_t s = m.fix_list[d.np + q];
+            fixup_lane(d, s, t.head);
+            search_lane(d, s, t.head);
+            d.st[st_index(s, F_FLAGS)] &= ~FL_FIXUP;
+        }
+}
+
 } // namespace
 
 extern "C" {
@@ -141,11 +185,17 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
                   size_t n_chunk_sizes, int invert, m17b_frame* out, size_t cap)
 {
     const bool streaming = (invert & 2) != 0;
+    const bool split = (invert & 4) != 0;          // streaming with the two chains of rounds run independently
+    uint32_t lcg = (uint32_t) (invert >> 8) * 2654435761u + 12345u;      // interleaving seed
     invert &= 1;
     uint32_t max_chunk = 0;
     for (size_t i = 0; i != n_chunk_sizes; ++i) max_chunk = std::max(max_chunk, chunk_sizes[i]);
     Emu m;
-    init(m, (uint32_t) n_streams, max_chunk, cap);
+    init(m, (uint32_t) n_streams, max_chunk, cap, split ? 4u : 1u);
+    std::vector<Task> pending[2];                  // rounds enqueued and not yet run, per chain, in order
+    uint32_t submit_no = 0;
+    auto run_one = [&](int c) { chain_round(m, pending[c].front(), max_chunk); pending[c].erase(pending[c].begin()); };
+    auto rnd = [&]() { lcg = lcg * 1664525u + 1013904223u; return lcg >> 16; };
     // matched filter over the whole capture in the reference's order (FirFilter.h:28-43)
     std::vector<float> x(n_streams * n), y(n_streams * n);
     for (size_t s = 0; s != n_streams; ++s) {
@@ -167,6 +217,11 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
     const DevPtrs& d = m.d;
     while (off < n) {
         uint32_t c = (uint32_t) std::min<size_t>(chunk_sizes[ci++ % n_chunk_sizes], n - off);
+        if (split) {
+            // the front end of submit k waits for the rounds of submit k - 2, both chains (m17b_submit: ev_rounds / ev_aux_rounds)
+            for (int ch = 0; ch != 2; ++ch)
+                while (!pending[ch].empty() && pending[ch].front().submit + 2 <= submit_no) run_one(ch);
+        }
         for (size_t s = 0; s != n_streams; ++s)
             for (uint32_t i = 0; i != c; ++i) {
                 size_t o = ring_off(m.head + i, d.ring_lines - 1, d.np, (uint32_t) s);
@@ -180,6 +235,19 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
         for (uint32_t s = 0; s != d.n_streams; ++s) { dcd_lane(d, s, 0, m.head, c, m.head64); dcd_lane(d, s, 1, m.head, c, m.head64); }
         m.head += c; m.head64 += c; off += c;
         int rounds = (int) (c / kMinFrameSpacing) + 2;
+        if (split) {
+            for (int ch = 0; ch != 2; ++ch)
+                for (int r = 0; r != rounds; ++r) pending[ch].push_back(Task{ch, m.head, m.head64, submit_no});
+            ++submit_no;
+            // the two chains make progress in an arbitrary interleaving; either may fall behind by up to two submits
+            for (uint32_t k = rnd() % (uint32_t) (4 * rounds + 1); k != 0; --k) {
+                int ch = (int) (rnd() & 1u);
+                if (pending[ch].empty()) ch ^= 1;
+                if (pending[ch].empty()) break;
+                run_one(ch);
+            }
+            continue;
+        }
         // flags bit 1 = M17B_STREAMING: lanes may leave a partial frame for the next submit; only the
         // final flush (m17b_sync) brings every lane to the head
         for (int r = 0; r != rounds; ++r) round(m, streaming);
@@ -187,6 +255,14 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
             if (extra == 256) return -1;
             round(m, streaming);
         }
+    }
+    if (split) {
+        while (!pending[0].empty() || !pending[1].empty()) {
+            int ch = (int) (rnd() & 1u);
+            if (pending[ch].empty()) ch ^= 1;
+            run_one(ch);
+        }
+        round(m, false);                           // m17b_sync's flush rounds: one classification, every stream to the head
     }
     for (int extra = 0; m.ctr.cls[1].lagging != 0 || m.ctr.cls[1].deferred != 0; ++extra) {
         if (extra == 256) return -1;

@@ -21,8 +21,10 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
-def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, streaming: bool = False, origin: int = 0) -> list[np.ndarray]:
-    """Run the emulated scan/decode lanes over [n_streams, n] int16 fed in submits of the given sizes."""
+def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, streaming: bool = False, origin: int = 0,
+          split_seed: int | None = None) -> list[np.ndarray]:
+    """Run the emulated scan/decode lanes over [n_streams, n] int16 fed in submits of the given sizes.  split_seed: emulate
+    M17B_STREAMING's two independent chains of rounds (receiving / acquiring streams) in a seeded arbitrary interleaving."""
     lib().m17emu_set_origin(ctypes.c_uint32(origin & 0xFFFFFFFF))
     from m17_cxx_demod_b200.demod import FRAME_DTYPE, split_by_stream
     samples = np.ascontiguousarray(samples, dtype=np.int16)
@@ -31,7 +33,7 @@ def demod(samples: np.ndarray, chunks, invert: bool = False, rec_dtype=None, str
     cap = ns * (2 * (n // 1600 + 2) + 8)
     out = np.zeros(cap, dtype=FRAME_DTYPE)
     k = lib().m17emu_demod(samples.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(ns), ctypes.c_size_t(n), ctypes.c_size_t(n),
-                           cs.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(cs)), ctypes.c_int(int(invert) | (2 if streaming else 0)),
+                           cs.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(cs)), ctypes.c_int(int(invert) | (2 if streaming else 0) | ((4 | ((split_seed & 0xFFFF) << 8)) if split_seed is not None else 0)),
                            out.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(cap))
     if k < 0:
         raise RuntimeError(f"m17emu_demod failed: {k}")

@@ -51,6 +51,20 @@ def test_emulated_lanes_streaming_deferral(mode):
         check(want, got, f"streaming mode {mode} chunks {chunks}")
 
 
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_emulated_lanes_two_independent_chains(seed):
+    """M17B_STREAMING as m17b_submit enqueues it: the receiving and the acquiring streams have a chain of rounds each,
+    every round classifies for itself, a stream changes chains through its flags word (an acquiring stream stops at the
+    start of a frame and after its walk budget; a receiving one that loses sync or needs the fix-up kernels becomes
+    acquiring), and either chain may be up to two submits behind.  Whatever the interleaving, the records must not change."""
+    x = gen.generate(random_params(400 + seed, gen.MIXED, 16), 96000)
+    want, _ = ol.demod_batch("port", x)
+    for chunks in ([9600], [4800, 2500], [1920, 3000, 7777]):
+        got = emu_lib.demod(x, chunks, streaming=True, split_seed=seed)
+        check(want, got, f"split chains seed {seed} chunks {chunks}")
+    assert sum(len(r) for r in want) > 100
+
+
 def test_emulated_lanes_across_the_32_bit_position_wrap():
     """Ring positions are uint32: a stream that starts 30,016 samples before 2^32 decodes across the wrap unchanged."""
     x = gen.generate(random_params(51, gen.MIXED, 12), 96000)
