@@ -356,11 +356,13 @@ void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, bool 
     classify_kernel<<<(d.np + 255) / 256, 256, 0, s>>>(d, head, class_mask, defer ? 1 : 0);
 }
 
-// The acquiring streams (class 1) are few and each is in a different part of the state machine: 32 of them in
-// a warp run one after the other (3 of 32 lanes active per instruction, measured), and the round waits for the
-// slowest warp.  They are spread over kSpread times as many warps instead, every kSpread-th lane active, which
-// divides a warp's serial chain by as much.
-constexpr int kSpread = 1;
+// The acquiring streams (class 1) are few and each is in a different part of the state machine: 32 of them in a
+// warp run one after the other (2-3 of 32 lanes active per instruction, measured).  They are spread over kSpread
+// times as many warps instead, every kSpread-th lane active, which shortens a warp's serial chain.  What bounds a
+// round of theirs is the slowest single lane (a whole preamble in ST_LSF_SYNC: correlations and estimator updates on
+// every symbol), so the gain is modest: configs[3] 23.0 -> 21.6 ms per step with 4, 22.1 with 8; the steady
+// configs[2] run is unchanged (12.2-12.4).
+constexpr int kSpread = 4;
 
 __global__ void __launch_bounds__(kScanThreads)
 scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls, int split)

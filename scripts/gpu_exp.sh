@@ -7,7 +7,7 @@ d=json.load(open("gpurun_out/exp_$tag.json"))
 print("$tag", round(d["value"]), round(d["ms_per_step"],2), {k:round(v,2) for k,v in d["kernel_ms_per_step"].items()}, d.get("parity",{}).get("mismatching"), d["faults"])
 PY
 }
-run pad6 M17B_FIR_PAD_KB=6
-run pad30 M17B_FIR_PAD_KB=30
-run aux6 M17B_AUX_ROUNDS=6
-run main6 M17B_MAIN_ROUNDS=6
+for sp in 1 4 8; do
+run d20_spread$sp M17B_SPREAD=$sp
+EXTRA="--workload c4" run c4_spread$sp M17B_SPREAD=$sp
+done
