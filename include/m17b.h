@@ -275,7 +275,7 @@ int  m17b_debug_correlate(m17b_ctx* ctx, const int16_t* samples_host, size_t n, 
  * m17b_debug_filter (scaling + 150-tap RRC, zero history, filter mode from `flags`: 0, M17B_FIR_FMA, M17B_INVERT) for
  * callers that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.
  * It calls no cudaMalloc / cudaFree / allocating routine and needs no m17b_ctx: the kernel's scratch (its temporary
- * sample ring, 5,283,840 bytes) is a static __device__ array that every GPU which loads the library holds until exit.
+ * sample ring, 3,186,688 bytes) is a static __device__ array that every GPU which loads the library holds until exit.
  * Hence the limits: n_streams <= M17B_NOALLOC_MAX_STREAMS and n <= M17B_NOALLOC_MAX_SAMPLES, beyond which it returns
  * M17B_ETOOBIG (use m17b_debug_filter).  Inputs and outputs are the caller's DEVICE buffers on `device`:
  * samples_device[s * stream_stride + 0 .. n) int16, filtered_device [n_streams][n] float.  The work is enqueued on

@@ -227,7 +227,7 @@ void free_all(m17b_ctx* c)
     for (auto& e : c->marks) if (e) cudaEventDestroy(e);
     for (auto& e : c->done) if (e) cudaEventDestroy(e);
     if (c->snap) cudaFreeHost(c->snap);
-    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_d); cudaFree(c->d.ring_x); cudaFree(c->d.mask_ring); cudaFree(c->d.ckpt_ring);
+    cudaFree(c->d.st); cudaFree(c->d.ring_y); cudaFree(c->d.ring_x); cudaFree(c->d.mask_ring); cudaFree(c->d.ckpt_ring);
     cudaFree(c->d.corr_snap); cudaFree(c->d.seg_ring); cudaFree(c->d.fix_list); cudaFree(c->d.scan_list); cudaFree(c->d.dec_list); cudaFree(c->d.diag_recs);
     cudaFree(c->d.sw_samples); cudaFree(c->d.fir_snap); cudaFree(c->d.llr); cudaFree(c->d.dec_bytes);
     cudaFree(c->d.recs); cudaFree(c->d.ctr); cudaFree(c->d.pkt_buf); cudaFree(c->d.pkt_recs);
@@ -338,7 +338,6 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         size_t ring_bytes = (size_t) d.ring_lines * np * kLine * sizeof(float);
         CK(cudaMalloc(&d.st, (np / 32) * NFIELDS * 32 * sizeof(uint32_t)));
         CK(cudaMalloc(&d.ring_y, ring_bytes));
-        CK(cudaMalloc(&d.ring_d, ring_bytes));
         CK(cudaMalloc(&d.ring_x, ring_bytes / 2));
         CK(cudaMalloc(&d.mask_ring, (size_t) d.ring_lines * np * 4 * sizeof(uint32_t)));
         CK(cudaMalloc(&d.ckpt_ring, (size_t) d.ring_lines * np * 4 * sizeof(float2)));
@@ -366,7 +365,6 @@ int m17b_create(const m17b_config* cfg, m17b_ctx** out)
         CK(cudaMalloc(&d.recs, (size_t) d.rec_cap * sizeof(m17b_frame)));
         CK(cudaMalloc(&d.ctr, sizeof(Counters)));
         CK(cudaMemsetAsync(d.ring_y, 0, ring_bytes, c->compute));
-        CK(cudaMemsetAsync(d.ring_d, 0, ring_bytes, c->compute));
         CK(cudaMemsetAsync(d.ring_x, 0, ring_bytes / 2, c->compute));
         CK(cudaMemsetAsync(d.mask_ring, 0, (size_t) d.ring_lines * np * 4 * sizeof(uint32_t), c->compute));
         CK(cudaMemsetAsync(d.ckpt_ring, 0, (size_t) d.ring_lines * np * 4 * sizeof(float2), c->compute));
@@ -483,12 +481,12 @@ int m17b_submit(m17b_ctx* c, const int16_t* samples, size_t n, size_t stride, in
         ev_begin(c, fs, CAT_AUX, p);
         launch_tail(c->d, dev_in, dev_stride, (uint32_t) n, c->tail[c->cur_tail], c->tail[c->cur_tail ^ 1], fs);
         ev_end(c, fs, p);
-        if (location == M17B_HOST) CK(cudaEventRecord(c->stage_free[c->cur_stage ^ 1], fs));
     }
-    // carrier-detect pre-pass over the new samples (reads ring_d written by the filter)
+    // carrier-detect pre-pass over the new samples (reads the same int16 input and the raw history the filter read)
     ev_begin(c, fs, CAT_DCD, p);
-    launch_dcd(c->d, c->head, (uint32_t) n, c->head64, fs);
+    launch_dcd(c->d, dev_in, dev_stride, c->tail[c->cur_tail], c->head, (uint32_t) n, c->head64, c->cfg.flags & M17B_INVERT, fs);
     ev_end(c, fs, p);
+    if (location == M17B_HOST) CK(cudaEventRecord(c->stage_free[c->cur_stage ^ 1], fs));      // the staging buffer may be refilled
     c->prof.dcd_launches += 1;
     if (streaming) {
         CK(cudaEventRecord(c->ev_front, fs));
@@ -777,7 +775,6 @@ static int debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size
     float *dy = nullptr, *dx = nullptr, *dcorr = nullptr;
     int rc = [&]() -> int {
         CK(cudaMalloc(&t.ring_y, ring_bytes));
-        CK(cudaMalloc(&t.ring_d, ring_bytes));
         CK(cudaMalloc(&t.ring_x, ring_bytes / 2));
         CK(cudaMalloc(&din, (size_t) ns * n * sizeof(int16_t)));
         CK(cudaMalloc(&dtail, (size_t) ns * kTailLen * sizeof(int16_t)));
@@ -800,7 +797,7 @@ static int debug_filter(m17b_ctx* c, const int16_t* samples_host, size_t n, size
         CK(cudaStreamSynchronize(c->compute));
         return M17B_OK;
     }();
-    cudaFree(t.ring_y); cudaFree(t.ring_d); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx); cudaFree(dcorr);
+    cudaFree(t.ring_y); cudaFree(t.ring_x); cudaFree(din); cudaFree(dtail); cudaFree(dy); cudaFree(dx); cudaFree(dcorr);
     return rc;
 }
 

@@ -2,18 +2,18 @@
 //
 // Data layout in HBM (N = streams padded to a multiple of 128, "Np"):
 //
-//   sample ring   ring_y / ring_d : float [RL lines][Np][32]
+//   sample ring   ring_y : float [RL lines][Np][32]
 //       line l of stream s holds samples 32l .. 32l+31 (128 B = one L2 line, four
-//       32-byte sectors).  ring_y = matched filter output computed speculatively
-//       for every sample; ring_d = x[n] - x[n-120], the input of the carrier
-//       detect's sliding DFT (SlidingDFT.h:123-124), where x is the scaled input
-//       (apps/m17-demod.cpp:489).  The lanes of a scan warp sit at different
+//       32-byte sectors): the matched filter output computed speculatively
+//       for every sample.  The lanes of a scan warp sit at different
 //       stream positions (each stops at its own frame completions), so a lane must
 //       own whole lines: it consumes the four sectors of a line in four consecutive
 //       8-sample blocks (one DRAM fetch, three L2 hits).  With 8-sample lines
 //       interleaved over streams (the first layout) every sector read dragged in
 //       three neighbours' sectors that were evicted before their lanes got there:
-//       3.6x the algorithmic DRAM traffic (profiles/r01b_*).
+//       3.6x the algorithmic DRAM traffic (profiles/r01b_*).  (Round 1 kept a second such
+//       ring for x[n] - x[n-120], the carrier detect's input; dcd_kernel now forms it
+//       from the int16 input.)
 //                 ring_x : int16 [RL][Np][32]  raw (sign-corrected) input, only for the
 //       rare paths that rebuild filter history after a carrier-detect gap.
 //   per-stream scalars            : uint32 [Np/32][NFIELDS][32]   (one coalesced
@@ -130,7 +130,6 @@ struct Counters {                 // device-side mirror of m17b_counters (+ reco
 struct DevPtrs {
     uint32_t* st;                 // [Np/32][NFIELDS][32]
     float* ring_y;                // [RL][Np][32]
-    float* ring_d;                // [RL][Np][32]
     int16_t* ring_x;              // [RL][Np][32]
     uint32_t* mask_ring;          // [RL][Np][4] sync-word trigger masks, one word per 8-sample block
     float* corr_snap;             // [80][Np] the correlator's last 80 samples before a carrier-detect gap
@@ -194,7 +193,8 @@ void launch_fir(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_n
                 uint32_t head, bool fma, bool invert, cudaStream_t s);
 void launch_tail(const DevPtrs& d, const int16_t* in, size_t stride, uint32_t n_new, const int16_t* tail_in,
                  int16_t* tail_out, cudaStream_t s);
-void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s);
+void launch_dcd(const DevPtrs& d, const int16_t* in, size_t stride, const int16_t* tail, uint32_t head_old, uint32_t n_new,
+                unsigned long long head64_old, bool invert, cudaStream_t s);
 void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, bool defer, cudaStream_t s);
 void launch_scan(const DevPtrs& d, uint32_t head, unsigned long long head64, bool defer, uint32_t guard, int cls, bool split, cudaStream_t s);
 void launch_decode(const DevPtrs& d, uint32_t head, unsigned long long head64, int cls, cudaStream_t s);

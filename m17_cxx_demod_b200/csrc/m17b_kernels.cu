@@ -182,19 +182,14 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
         for (int r = 0; r != kFirOut / 2; ++r)
             asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[2 * r]), "=f"(acc[2 * r + 1]) : "l"(acc2[r].v));
 
-        // 16 outputs = two 8-sample blocks; a block never straddles a 32-sample ring line.  Besides y:
-        // d = x[n] - x[n-120] (the sliding DFT's `sample - oldest`, SlidingDFT.h:123-124; the 160-sample
-        // halo covers the look-back) and the raw sample as int16 (exact inverse of the scaling).
+        // 16 outputs = two 8-sample blocks; a block never straddles a 32-sample ring line.  Besides y: the raw
+        // sample as int16 (exact inverse of the scaling), for the rare paths that rebuild filter history.
 #pragma unroll
         for (int k = 0; k != kFirOut / 8; ++k) {
             const uint32_t p = tb + (uint32_t) o0 + 8u * k;
             const size_t o = ((size_t) ((p >> 5) & lmask) * d.np + s) * kLine + (p & (kLine - 1));
             float4* py = reinterpret_cast<float4*>(d.ring_y + o);
-            float4* pd = reinterpret_cast<float4*>(d.ring_d + o);
-            float dl[8];
             uint32_t raw[4];
-#pragma unroll
-            for (int i = 0; i != 8; ++i) dl[i] = __fsub_rn(row[8 * k + i], row[8 * k + i - kDftN]);
 #pragma unroll
             for (int i = 0; i != 4; ++i) {
                 int lo = __float2int_rn(__fmul_rn(row[8 * k + 2 * i], 41067.0f));
@@ -209,15 +204,12 @@ fir_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, uint32_t n_
                 for (int i = 0; i != 8; ++i)
                     if ((int) (p + (uint32_t) i - head) >= 0) {
                         d.ring_y[o + i] = acc[8 * k + i];
-                        d.ring_d[o + i] = dl[i];
                         d.ring_x[o + i] = (int16_t) ((i & 1) ? (raw[i >> 1] >> 16) : (raw[i >> 1] & 0xFFFFu));
                     }
                 continue;
             }
             py[0] = make_float4(acc[8 * k + 0], acc[8 * k + 1], acc[8 * k + 2], acc[8 * k + 3]);
             py[1] = make_float4(acc[8 * k + 4], acc[8 * k + 5], acc[8 * k + 6], acc[8 * k + 7]);
-            pd[0] = make_float4(dl[0], dl[1], dl[2], dl[3]);
-            pd[1] = make_float4(dl[4], dl[5], dl[6], dl[7]);
             *reinterpret_cast<uint4*>(d.ring_x + o) = make_uint4(raw[0], raw[1], raw[2], raw[3]);
         }
     }
@@ -287,19 +279,81 @@ namespace m17b {
 
 constexpr int kScanThreads = 128;
 
-// Carrier-detect pre-pass (dcd_lane) over the new samples of a submit, all lanes
-// at the same position, two lanes (one per DFT bin) per stream.  Bound: FP32 issue; reads ring_d once (4 B/sample).
+// dcd_lane's sample source on the device: x[n] - x[n-120] from the submit's int16 input and the raw history tail.
+// The two lanes of a stream (one per DFT bin) share the work of a whole block inside the submit: each loads,
+// scales and subtracts four of its eight samples (8-byte loads; x[n-120] is 15 blocks back, in the same row or in
+// the tail, never straddling the two) and hands them to its partner by shuffle.  Blocks that stick out of the
+// submit, and every block of a submit whose rows are not 16-byte aligned, take the scalar path.
+struct DcdSrc {
+    const int16_t* row;        // the stream's new samples: row[0 .. n_new)
+    const int16_t* trow;       // one past the stream's raw history: trow[-160 .. 0)
+    uint32_t head_old, n_new, mask;
+    int half, invert, aligned;
+    int rel0;
+    bool fast;
+    uint2 cur, old;
+    __device__ __forceinline__ float sx(int v) const { return scale_i16(invert ? (int) (int16_t) (-v) : v); }
+    __device__ __forceinline__ void request(uint32_t base)
+    {
+        rel0 = (int) (base - head_old);
+        fast = aligned && rel0 >= 0 && (uint32_t) rel0 + 8u <= n_new;
+        if (fast) {
+            const int r = rel0 + 4 * half, ro = r - kDftN;
+            cur = *reinterpret_cast<const uint2*>(row + r);
+            old = *reinterpret_cast<const uint2*>((ro >= 0 ? row : trow) + ro);
+        }
+    }
+    __device__ __forceinline__ void take(float (&dl)[8])
+    {
+        if (fast) {
+            const uint32_t c[2] = {cur.x, cur.y}, o[2] = {old.x, old.y};
+            float v[4], w[4];
+#pragma unroll
+            for (int i = 0; i != 4; ++i) {
+                const int xc = (int) (int16_t) ((i & 1) ? (c[i >> 1] >> 16) : (c[i >> 1] & 0xFFFFu));
+                const int xo = (int) (int16_t) ((i & 1) ? (o[i >> 1] >> 16) : (o[i >> 1] & 0xFFFFu));
+                v[i] = __fsub_rn(sx(xc), sx(xo));
+            }
+#pragma unroll
+            for (int i = 0; i != 4; ++i) w[i] = __shfl_xor_sync(mask, v[i], 1);
+#pragma unroll
+            for (int i = 0; i != 4; ++i) { dl[i] = half ? w[i] : v[i]; dl[4 + i] = half ? v[i] : w[i]; }
+        } else {
+#pragma unroll
+            for (int j = 0; j != 8; ++j) {
+                const int r = rel0 + j, ro = r - kDftN;
+                float v = 0.f;
+                if (r >= 0 && (uint32_t) r < n_new) v = __fsub_rn(sx(row[r]), sx(ro >= 0 ? row[ro] : trow[ro]));
+                dl[j] = v;
+            }
+        }
+    }
+};
+
+// Carrier-detect pre-pass (dcd_lane) over the new samples of a submit, all lanes at the same position, two lanes (one
+// per DFT bin) per stream.  Bound: FP32 issue; reads the int16 input once from DRAM (2 B/sample).
 __global__ void __launch_bounds__(128)
-dcd_kernel(DevPtrs d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old)
+dcd_kernel(DevPtrs d, const int16_t* __restrict__ in, size_t stride, const int16_t* __restrict__ tail, uint32_t head_old, uint32_t n_new,
+           unsigned long long head64_old, int invert, int aligned)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;      // lane pair = the two bins of one stream
     if ((t >> 1) >= d.n_streams) return;
-    dcd_lane(d, t >> 1, (int) (t & 1u), head_old, n_new, head64_old);
+    const uint32_t s = t >> 1;
+    DcdSrc src;
+    src.row = in + (size_t) s * stride;
+    src.trow = tail + (size_t) s * kTailLen + kTailLen;
+    src.head_old = head_old; src.n_new = n_new; src.mask = __activemask();
+    src.half = (int) (t & 1u); src.invert = invert; src.aligned = aligned;
+    dcd_lane(d, s, (int) (t & 1u), head_old, n_new, head64_old, src);
 }
 
-void launch_dcd(const DevPtrs& d, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, cudaStream_t s)
+void launch_dcd(const DevPtrs& d, const int16_t* in, size_t stride, const int16_t* tail, uint32_t head_old, uint32_t n_new,
+                unsigned long long head64_old, bool invert, cudaStream_t s)
 {
-    dcd_kernel<<<(2 * d.n_streams + 127) / 128, 128, 0, s>>>(d, head_old, n_new, head64_old);
+    // 8-byte loads need the submit to start on a ring-block boundary and 16-byte aligned rows (like the filter's)
+    const int aligned = (head_old % 8 == 0) && (stride % 8 == 0) && (reinterpret_cast<uintptr_t>(in) % 16 == 0) &&
+                        (reinterpret_cast<uintptr_t>(tail) % 16 == 0);
+    dcd_kernel<<<(2 * d.n_streams + 127) / 128, 128, 0, s>>>(d, in, stride, tail, head_old, n_new, head64_old, invert ? 1 : 0, aligned);
 }
 
 // Which streams have samples to walk this round, and how: the lanes of a warp run in lock-step, so a warp moves at

@@ -936,7 +936,14 @@ M17B_FN void bq_feed(Biquad& b, const float (&y)[8], int jb, int je)
 // ---------------------------------------------------------------------------
 // One lane = one DFT bin of one stream (bin 0 or 1: the two bins and their sums are independent
 // recurrences, so a stream is split over two neighbouring lanes that read the same samples).
-M17B_FN void dcd_lane(const DevPtrs& d, uint32_t s, int bin, uint32_t head_old, uint32_t n_new, unsigned long long head64_old)
+// The sliding DFT's input x[n] - x[n-120] (SlidingDFT.h:123-124, x = the scaled sample, apps/m17-demod.cpp:489) is
+// formed here from the submit's own int16 samples and the raw history tail (`src`: DcdSrc in m17b_kernels.cu, a
+// scalar stand-in in tests/emu) -- round 1's matched filter wrote it to a second float ring (4 B/sample of DRAM
+// traffic each way and a third of the ring memory).  src.request(base) asks for the 8-sample block at ring position
+// `base` (any block that overlaps [head_old, head_old + n_new), or the one after), src.take(dl) delivers it; values
+// of samples outside the submit are unspecified and unused.
+template <class Src>
+M17B_FN void dcd_lane(const DevPtrs& d, uint32_t s, int bin, uint32_t head_old, uint32_t n_new, unsigned long long head64_old, Src& src)
 {
     uint32_t* sb = d.st + st_index(s, 0);
     const int f_re = bin ? F_RE1 : F_RE0, f_im = bin ? F_IM1 : F_IM0, f_first = bin ? F_L2 : F_L1, f_acc = bin ? F_ACC2 : F_ACC1;
@@ -949,13 +956,13 @@ M17B_FN void dcd_lane(const DevPtrs& d, uint32_t s, int bin, uint32_t head_old, 
     uint32_t seg = (uint32_t) (head64_old / kSeg);       // ordinal of the segment the next sample is in
     uint32_t age = (uint32_t) (head64_old % kSeg);
     uint32_t m5 = seg % 5u;
-    const uint32_t lmask = d.ring_lines - 1, smask = d.n_seg - 1;
+    const uint32_t smask = d.n_seg - 1;
     const size_t np = d.np;
     float* const ring = d.seg_ring + (size_t) bin * np + s;       // slot k = bin (@384) / 2 + bin (@960)
     // per sample: SlidingDFT.h:118-132 for this bin, its energy (DataCarrierDetect.h:53-58), the sums
 #define M17B_DCD_STEP(x_)                                                        \
     do {                                                                         \
-        const float a_ = re + (x_), b_ = im;   /* x_ = sample - oldest, formed by fir_kernel */ \
+        const float a_ = re + (x_), b_ = im;   /* x_ = sample - oldest */       \
         re = a_ * cr - b_ * ci; im = a_ * ci + b_ * cr;                          \
         const float e_ = re * re + im * im;                                      \
         if (in_first) first += e_;                                               \
@@ -977,13 +984,11 @@ M17B_FN void dcd_lane(const DevPtrs& d, uint32_t s, int bin, uint32_t head_old, 
     bool in_first = seg < (uint32_t) (kFirstUpdate / kSeg);
     const uint32_t n_blk = ((head_old & 7u) + n_new + 7u) >> 3;
     uint32_t base = head_old & ~7u;
-    const float4* pd = reinterpret_cast<const float4*>(d.ring_d + ring_off(base, lmask, d.np, s));
-    float4 q0 = pd[0], q1 = pd[1];
+    src.request(base);
     for (uint32_t b = 0; b != n_blk; ++b, base += 8u) {
-        const float dl[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-        // next block requested before this one's arithmetic (one block past the end is inside the ring)
-        pd = reinterpret_cast<const float4*>(d.ring_d + ring_off(base + 8u, lmask, d.np, s));
-        q0 = pd[0]; q1 = pd[1];
+        float dl[8];
+        src.take(dl);
+        src.request(base + 8u);                             // the next block's samples, before this one's arithmetic
         const uint32_t rel = base - head_old;               // wraps for the partial first block
         if (rel < n_new && n_new - rel >= 8u) {
             // whole block inside the submit; blocks are 8-aligned in stream time, so a segment can only end

@@ -3,7 +3,7 @@
 // No counterpart in the reference.  Some callers cannot call cudaMalloc
 // (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  m17b_debug_filter() runs fir_kernel
 // into a temporary sample ring it cudaMallocs per call; this variant keeps that ring -- fir_kernel's scratch: ring_y,
-// ring_d, ring_x and the zero filter history -- in ONE file-scope __device__ array of a fixed, modest size, so the
+// ring_x and the zero filter history -- in ONE file-scope __device__ array of a fixed, modest size, so the
 // entry point allocates nothing: no cudaMalloc / cudaFree / cudaHostAlloc, no allocating library routine.
 //
 // The array's name is a host-side stand-in in host code, not a device address: the address the kernels get comes from
@@ -25,12 +25,11 @@ static_assert(kMaxStreams == 128 && (kMaxSamples + kLine - 1) / kLine + 1 <= kLi
 
 constexpr size_t kRingFloats = (size_t) kLines * kMaxStreams * kLine;
 constexpr size_t kOffY = 0;
-constexpr size_t kOffD = kOffY + kRingFloats * sizeof(float);
-constexpr size_t kOffX = kOffD + kRingFloats * sizeof(float);
+constexpr size_t kOffX = kOffY + kRingFloats * sizeof(float);
 constexpr size_t kOffTail = kOffX + kRingFloats * sizeof(int16_t);
 constexpr size_t kTailBytes = (size_t) kMaxStreams * kTailLen * sizeof(int16_t);
-constexpr size_t kScratchBytes = kOffTail + kTailBytes;          // 5,283,840 bytes
-static_assert(kOffD % 256 == 0 && kOffX % 256 == 0 && kOffTail % 256 == 0, "256-byte aligned parts");
+constexpr size_t kScratchBytes = kOffTail + kTailBytes;          // 3,186,688 bytes
+static_assert(kScratchBytes == 3186688 && kOffX % 256 == 0 && kOffTail % 256 == 0, "256-byte aligned parts");
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
 
@@ -82,7 +81,6 @@ extern "C" int m17b_filter_noalloc(int device, const int16_t* samples_device, ui
     while (lines < (uint32_t) ((n + kLine - 1) / kLine + 1)) lines <<= 1;
     t.ring_lines = lines;                                            // <= kLines by the size check above
     t.ring_y = reinterpret_cast<float*>(scratch + kOffY);
-    t.ring_d = reinterpret_cast<float*>(scratch + kOffD);
     t.ring_x = reinterpret_cast<int16_t*>(scratch + kOffX);
     int16_t* tail = reinterpret_cast<int16_t*>(scratch + kOffTail);
     // the filter starts on zero history; the rings need no clearing (fir_kernel writes every position that is read back)

@@ -31,7 +31,7 @@ uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p
 struct Emu {
     DevPtrs d{};
     std::vector<uint32_t> st;
-    std::vector<float> ring_y, ring_d, corr_snap, sw_samples, fir_snap, seg_ring;
+    std::vector<float> ring_y, corr_snap, sw_samples, fir_snap, seg_ring;
     std::vector<float2> ckpt_ring;
     std::vector<int16_t> llr, ring_x;
     std::vector<uint32_t> fix_list, dec_list, mask_ring;
@@ -63,7 +63,6 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap, uint32
     size_t np = d.np;
     m.st.assign((np / 32) * NFIELDS * 32, 0);
     m.ring_y.assign((size_t) d.ring_lines * np * kLine, 0.f);
-    m.ring_d.assign((size_t) d.ring_lines * np * kLine, 0.f);
     m.ring_x.assign((size_t) d.ring_lines * np * kLine, 0);
     m.corr_snap.assign(80 * np, 0.f);
     m.mask_ring.assign((size_t) d.ring_lines * np * 4, 0);
@@ -81,7 +80,7 @@ void init(Emu& m, uint32_t n_streams, uint32_t max_chunk, size_t rec_cap, uint32
     d.pkt_cap = next_pow2(std::max<uint32_t>(64u, (uint32_t) np));
     m.pkt_recs.resize(d.pkt_cap);
     d.pkt_buf = m.pkt_buf.data(); d.pkt_recs = m.pkt_recs.data(); d.pkt_read = 0;
-    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_d = m.ring_d.data(); d.ring_x = m.ring_x.data(); d.corr_snap = m.corr_snap.data();
+    d.st = m.st.data(); d.ring_y = m.ring_y.data(); d.ring_x = m.ring_x.data(); d.corr_snap = m.corr_snap.data();
     d.mask_ring = m.mask_ring.data(); d.ckpt_ring = m.ckpt_ring.data(); d.seg_ring = m.seg_ring.data(); d.fix_list = m.fix_list.data(); d.dec_list = m.dec_list.data(); d.sw_samples = m.sw_samples.data(); d.fir_snap = m.fir_snap.data();
     d.llr = m.llr.data(); d.dec_bytes = m.dec_bytes.data(); d.recs = m.recs.data(); d.ctr = &m.ctr;
     for (uint32_t s = 0; s != d.np; ++s) init_lane(d.st + st_index(s, 0), g_origin);
@@ -229,10 +228,25 @@ long m17emu_demod(const int16_t* samples, size_t n_streams, size_t n, size_t str
                 int v = samples[s * stride + t];
                 if (invert) v = (int) (int16_t) (-v);
                 m.ring_y[o] = y[s * n + t];
-                m.ring_d[o] = x[s * n + t] - (t >= (size_t) kDftN ? x[s * n + t - kDftN] : 0.f);
                 m.ring_x[o] = (int16_t) v;
             }
-        for (uint32_t s = 0; s != d.n_streams; ++s) { dcd_lane(d, s, 0, m.head, c, m.head64); dcd_lane(d, s, 1, m.head, c, m.head64); }
+        for (uint32_t s = 0; s != d.n_streams; ++s) {
+            // dcd_lane's sample source (DcdSrc in m17b_kernels.cu), scalar: x[n] - x[n-120] from the int16 samples; before
+            // the first sample of the stream the raw history is zero
+            struct Src {
+                const int16_t* row; long long off; uint32_t head_old, n_new; int invert; int rel0;
+                float sx(long long t) const { int v = t >= 0 ? row[t] : 0; if (invert) v = (int) (int16_t) (-v); return scale_i16(v); }
+                void request(uint32_t base) { rel0 = (int) (base - head_old); }
+                void take(float (&dl)[8]) {
+                    for (int j = 0; j != 8; ++j) {
+                        const int r = rel0 + j;
+                        dl[j] = (r >= 0 && (uint32_t) r < n_new) ? sx(off + r) - sx(off + r - kDftN) : 0.f;
+                    }
+                }
+            } src{samples + s * stride, (long long) off, m.head, c, invert, 0};
+            dcd_lane(d, s, 0, m.head, c, m.head64, src);
+            dcd_lane(d, s, 1, m.head, c, m.head64, src);
+        }
         m.head += c; m.head64 += c; off += c;
         int rounds = (int) (c / kMinFrameSpacing) + 2;
         if (split) {
