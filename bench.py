@@ -371,7 +371,7 @@ def main():
                 "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_peak if gbs else None, "bound": "latency (dependent issue), not HBM"}
     roofline_hbm = {
         "peak_gbs": hbm_peak, "peak_source": hbm_src,
-        "dcd": hbm_entry(4.0 * samples_step, prof.dcd_ms / P, prof.dcd_launches / P, "4 B/sample read (x[n] - x[n-120])"),
+        "dcd": hbm_entry(2.0 * samples_step, prof.dcd_ms / P, prof.dcd_launches / P, "2 B/sample read (the int16 input; x[n-120] comes from the same rows again, out of L1 / L2)"),
         "scan": hbm_entry(4.0 * samples_step + 368.0 * frames_step, (prof.scan_ms + prof.scan1_ms) / P, prof.scan_launches / P,
                           "4 B/sample read (matched-filter output) + 368 B/frame written (soft bits)"),
         "decode": hbm_entry((368.0 + 80.0) * frames_step, prof.decode_ms / P, prof.decode_launches / P,
