@@ -416,7 +416,15 @@ void launch_classify(const DevPtrs& d, uint32_t head, uint32_t class_mask, bool 
 // round of theirs is the slowest single lane (a whole preamble in ST_LSF_SYNC: correlations and estimator updates on
 // every symbol), so the gain is modest: configs[3] 23.0 -> 21.6 ms per step with 4, 22.1 with 8; the steady
 // configs[2] run is unchanged (12.2-12.4).
+// Only while the spread-out lanes still fit the machine in one wave (148 SMs x 16 resident warps of this kernel): with
+// more acquiring streams than that (configs[3] at 131,072 channels: 40,000 of them) the extra warps are a second wave and
+// cost more than the shorter chains save (39.2 against 35.5 ms per step), so the factor falls to 2 and to 1.
 constexpr int kSpread = 4;
+constexpr uint32_t kSpreadThreads = 148u * 16u * 32u;
+__device__ __forceinline__ uint32_t spread_for(uint32_t n)
+{
+    return n * 4u <= kSpreadThreads ? 4u : n * 2u <= kSpreadThreads ? 2u : 1u;
+}
 
 __global__ void __launch_bounds__(kScanThreads)
 scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint32_t guard, int cls, int split)
@@ -424,9 +432,9 @@ scan_kernel(DevPtrs d, uint32_t head, unsigned long long head64, int defer, uint
     __shared__ LlrTable tab;                               // lanes look up different entries: shared, not constant memory
     const int tid = threadIdx.x;
     const uint32_t t = blockIdx.x * kScanThreads + tid;
-    const uint32_t spread = cls ? (uint32_t) kSpread : 1u;
-    const uint32_t g = t / spread;                         // thread takes the g-th entry of the class's list
     const uint32_t n = d.ctr->cls[cls].scan_count;
+    const uint32_t spread = cls ? spread_for(n) : 1u;
+    const uint32_t g = t / spread;                         // thread takes the g-th entry of the class's list
     if (blockIdx.x * kScanThreads / spread >= n) return;   // CTA-uniform
     for (int i = tid; i < 48; i += kScanThreads) tab.thr[i] = llr_thr_padded(c_tab.llr_thr, i);
     for (int i = tid; i < 43; i += kScanThreads) {
